@@ -1,0 +1,45 @@
+// crocoddyl_b200 — shared device/host definitions of the batched DDP/FDDP path.
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace cgx {
+
+// Thresholds and constants of SolverAbstract / SolverDDP / SolverFDDP
+// (reference: src/core/solver-base.cpp:14-25, src/core/solvers/ddp.cpp:17-36, fddp.cpp:15).
+struct SolverOpts {
+  double th_acceptstep, th_stop, th_grad, th_stepdec, th_stepinc, th_acceptnegstep;
+  double regfactor, regmin, regmax;
+  double alphas[16];
+  int nalphas;
+};
+
+// per-problem scalar slots (double), stored as scal[slot * Bp + b]
+enum {
+  S_COST = 0, S_STOP, S_D0, S_D1, S_XREG, S_UREG, S_STEP, S_DV, S_DVEXP, S_COST_TRY, S_DG, S_DQ, S_DVGAP, S_NSLOTS
+};
+// per-problem int slots, iscal[slot * Bp + b]
+enum {
+  I_ITER = 0, I_FEAS, I_WASFEAS, I_CONVERGED, I_CUR, I_NREC, I_BSTATUS, I_FSTATUS, I_NBWD, I_NFWD, I_NSLOTS
+};
+
+// raiseIfNaN (reference: src/core/solver-base.cpp:175-181)
+__host__ __device__ inline bool raise_if_nan(double v) { return isnan(v) || isinf(v) || v >= 1e30; }
+
+// increaseRegularization / decreaseRegularization (reference: src/core/solvers/ddp.cpp:312-326)
+__host__ __device__ inline void reg_increase(const SolverOpts& o, double& xreg, double& ureg) {
+  xreg *= o.regfactor;
+  if (xreg > o.regmax) xreg = o.regmax;
+  ureg = xreg;
+}
+__host__ __device__ inline void reg_decrease(const SolverOpts& o, double& xreg, double& ureg) {
+  xreg /= o.regfactor;
+  if (xreg < o.regmin) xreg = o.regmin;
+  ureg = xreg;
+}
+
+constexpr int NTRACE = 13;  // matches CGX_NTRACE
+
+}  // namespace cgx

@@ -1,0 +1,344 @@
+// crocoddyl_b200 — host driver of the thread-per-problem kernels (tpp.cuh). Model family: unicycle.
+#include <cstring>
+#include <map>
+#include "backend.hpp"
+#include "tpp.cuh"
+
+namespace cgx {
+
+namespace {
+
+template <class M>
+struct TppBackend : Backend {
+  static constexpr int N = M::NX, U = M::NU;
+  TppCtx c;
+  std::vector<void*> allocs;
+  bool solver_allocated = false;
+  double* node_data[9] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  double* tmp_xs = nullptr;  // SoA scratch for the problem-level API
+  double* tmp_us = nullptr;
+
+  explicit TppBackend(const ProblemDesc* p_, int sk) {
+    p = p_;
+    solver_kind = sk;
+    std::memset(&c, 0, sizeof(c));
+    c.B = p->B;
+    c.Bp = ((p->B + 63) / 64) * 64;
+    c.T = p->T;
+    c.fddp = sk == 1;
+    CGX_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 4; ++i) CGX_CUDA(cudaEventCreate(&ev[i]));
+    c.mparams = p->d_params;
+    c.x0 = alloc((size_t)N * c.Bp);
+    x0_changed();
+  }
+  ~TppBackend() override {
+    for (void* q : allocs) cudaFree(q);
+    for (int i = 0; i < 4; ++i)
+      if (ev[i]) cudaEventDestroy(ev[i]);
+    if (stream) cudaStreamDestroy(stream);
+  }
+  double* alloc(size_t n) {
+    double* q = dalloc<double>(n);
+    CGX_CUDA(cudaMemsetAsync(q, 0, n * sizeof(double), stream));
+    allocs.push_back(q);
+    return q;
+  }
+  void release(double*& q) {
+    if (!q) return;
+    for (size_t i = 0; i < allocs.size(); ++i)
+      if (allocs[i] == q) {
+        allocs.erase(allocs.begin() + i);
+        break;
+      }
+    cudaFree(q);
+    q = nullptr;
+  }
+  dim3 tgrid(int W, int nb) const { return dim3((nb + 31) / 32, (W + 31) / 32); }
+  void to_soa(const double* d_user, double* soa0, double* soa1, const int* cur, int flip, int W) {
+    tpp_transpose_kernel<<<tgrid(W, c.B), dim3(32, 8), 0, stream>>>(const_cast<double*>(d_user), soa0, soa1, cur,
+                                                                     flip, W, c.Bp, 0, c.B, 1);
+    ++last_launches;
+  }
+  void to_user(double* d_user, const double* soa0, const double* soa1, const int* cur, int flip, int W, int b0,
+               int nb) {
+    tpp_transpose_kernel<<<tgrid(W, nb), dim3(32, 8), 0, stream>>>(d_user, const_cast<double*>(soa0),
+                                                                    const_cast<double*>(soa1), cur, flip, W, c.Bp, b0,
+                                                                    nb, 0);
+    ++last_launches;
+  }
+  int nblocks() const { return (c.B + 63) / 64; }
+
+  void x0_changed() override {
+    to_soa(p->d_x0, c.x0, c.x0, nullptr, 0, N);
+    CGX_CUDA(cudaStreamSynchronize(stream));
+  }
+
+  void configure() override {
+    c.o = o;
+    const size_t Bp = c.Bp, T = c.T;
+    if (!solver_allocated) {
+      for (int i = 0; i < 2; ++i) {
+        c.xs[i] = alloc((T + 1) * N * Bp);
+        c.us[i] = alloc(T * U * Bp);
+      }
+      c.fs = alloc((T + 1) * N * Bp);
+      c.K = alloc(T * U * N * Bp);
+      c.k = alloc(T * U * Bp);
+      c.Vx = alloc((T + 1) * N * Bp);
+      c.Vxx = alloc((T + 1) * N * N * Bp);
+      c.w = alloc((T + 1) * N * Bp);
+      c.scal = alloc((size_t)S_NSLOTS * Bp);
+      int* is = dalloc<int>((size_t)I_NSLOTS * Bp);
+      allocs.push_back(is);
+      c.iscal = is;
+      CGX_CUDA(cudaMemsetAsync(is, 0, (size_t)I_NSLOTS * Bp * sizeof(int), stream));
+      // SolverAbstract ctor values (solver-base.cpp:14-25): xreg = ureg = NaN, steplength = 1
+      std::vector<double> h((size_t)S_NSLOTS * Bp, 0.);
+      for (size_t b = 0; b < Bp; ++b) {
+        h[(size_t)S_XREG * Bp + b] = NAN;
+        h[(size_t)S_UREG * Bp + b] = NAN;
+        h[(size_t)S_STEP * Bp + b] = 1.;
+      }
+      CGX_CUDA(cudaMemcpyAsync(c.scal, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice, stream));
+      CGX_CUDA(cudaStreamSynchronize(stream));
+      solver_allocated = true;
+    }
+    if (full && !c.Qxx) {
+      c.Qxx = alloc(T * N * N * Bp);
+      c.Qxu = alloc(T * N * U * Bp);
+      c.Quu = alloc(T * U * U * Bp);
+      c.Qx = alloc(T * N * Bp);
+      c.Qu = alloc(T * U * Bp);
+    }
+    c.full = full;
+    if (trace_on && (!c.trace || c.trace_cap != trace_cap)) {
+      release(c.trace);
+      c.trace = alloc((size_t)trace_cap * NTRACE * Bp);
+      c.trace_cap = trace_cap;
+    }
+    if (!trace_on) {
+      release(c.trace);
+      c.trace_cap = 0;
+    }
+  }
+
+  void set_candidate(const double* d_xs, const double* d_us, int is_feasible) override {
+    const size_t Bp = c.Bp, T = c.T;
+    tpp_reset_kernel<<<(c.Bp + 63) / 64, 64, 0, stream>>>(c, is_feasible);
+    ++last_launches;
+    if (d_xs)
+      to_soa(d_xs, c.xs[0], c.xs[0], nullptr, 0, (T + 1) * N);
+    else
+      CGX_CUDA(cudaMemsetAsync(c.xs[0], 0, (T + 1) * N * Bp * sizeof(double), stream));
+    if (d_us)
+      to_soa(d_us, c.us[0], c.us[0], nullptr, 0, T * U);
+    else
+      CGX_CUDA(cudaMemsetAsync(c.us[0], 0, T * U * Bp * sizeof(double), stream));
+  }
+
+  void solve(int maxiter, int is_feasible, double reginit) override {
+    c.o = o;
+    CGX_CUDA(cudaEventRecord(ev[1], stream));
+    tpp_solve_kernel<M><<<nblocks(), 64, 0, stream>>>(c, maxiter, is_feasible, reginit);
+    CGX_CUDA(cudaEventRecord(ev[2], stream));
+    ++last_launches;
+    CGX_CUDA(cudaGetLastError());
+  }
+  void compute_direction(int recalc) override {
+    c.o = o;
+    CGX_CUDA(cudaEventRecord(ev[1], stream));
+    tpp_direction_kernel<M><<<nblocks(), 64, 0, stream>>>(c, recalc);
+    CGX_CUDA(cudaEventRecord(ev[2], stream));
+    ++last_launches;
+    CGX_CUDA(cudaGetLastError());
+  }
+  void try_step(double alpha) override {
+    c.o = o;
+    CGX_CUDA(cudaEventRecord(ev[1], stream));
+    tpp_trystep_kernel<M><<<nblocks(), 64, 0, stream>>>(c, alpha);
+    CGX_CUDA(cudaEventRecord(ev[2], stream));
+    ++last_launches;
+    CGX_CUDA(cudaGetLastError());
+  }
+
+  struct Fld {
+    double* a;
+    double* b;  // second buffer for double-buffered fields
+    int flip;   // 0: candidate, 1: trial
+    int size, nt;
+    bool dbl;
+  };
+  Fld fld(const std::string& n) {
+    const int T = c.T;
+    if (n == "xs") return {c.xs[0], c.xs[1], 0, N, T + 1, true};
+    if (n == "xs_try") return {c.xs[0], c.xs[1], 1, N, T + 1, true};
+    if (n == "us") return {c.us[0], c.us[1], 0, U, T, true};
+    if (n == "us_try") return {c.us[0], c.us[1], 1, U, T, true};
+    if (n == "fs") return {c.fs, c.fs, 0, N, T + 1, false};
+    if (n == "K") return {c.K, c.K, 0, U * N, T, false};
+    if (n == "k") return {c.k, c.k, 0, U, T, false};
+    if (n == "Vx") return {c.Vx, c.Vx, 0, N, T + 1, false};
+    if (n == "Vxx") return {c.Vxx, c.Vxx, 0, N * N, T + 1, false};
+    if (n == "Qxx" || n == "Qxu" || n == "Quu" || n == "Qx" || n == "Qu") {
+      if (!c.full || !c.Qxx)
+        throw Unsupported("field " + n + " is not kept with cgx_solver_set_storage(full = 0)");
+      if (n == "Qxx") return {c.Qxx, c.Qxx, 0, N * N, T, false};
+      if (n == "Qxu") return {c.Qxu, c.Qxu, 0, N * U, T, false};
+      if (n == "Quu") return {c.Quu, c.Quu, 0, U * U, T, false};
+      if (n == "Qx") return {c.Qx, c.Qx, 0, N, T, false};
+      return {c.Qu, c.Qu, 0, U, T, false};
+    }
+    throw NotFound("unknown field " + n);
+  }
+  FieldInfo field_info(const std::string& name) override {
+    Fld f = fld(name);
+    return {f.size, f.nt};
+  }
+  void export_field(const std::string& name, int b0, int nb, double* d_out) override {
+    Fld f = fld(name);
+    to_user(d_out, f.a, f.b, f.dbl ? c.iscal + (size_t)I_CUR * c.Bp : nullptr, f.flip, f.size * f.nt, b0, nb);
+  }
+  void import_field(const std::string& name, const double* d_in) override {
+    if (name != "xs" && name != "us") throw Unsupported("only xs and us can be set");
+    Fld f = fld(name);
+    to_soa(d_in, f.a, f.b, c.iscal + (size_t)I_CUR * c.Bp, 0, f.size * f.nt);
+  }
+  void export_scalars(double* d_out) override;
+  void export_status(int which, int* d_out) override {
+    CGX_CUDA(cudaMemcpyAsync(d_out, c.iscal + (size_t)(which ? I_FSTATUS : I_BSTATUS) * c.Bp, c.B * sizeof(int),
+                             cudaMemcpyDeviceToDevice, stream));
+  }
+  void set_reg(double xreg, double ureg, bool set_x, bool set_u) override;
+  void export_trace(int b, double* d_out) override;
+
+  // ---- problem-level API ----
+  void ensure_tmp() {
+    if (!tmp_xs) {
+      tmp_xs = alloc((size_t)(c.T + 1) * N * c.Bp);
+      tmp_us = alloc((size_t)c.T * U * c.Bp);
+    }
+  }
+  void problem_calc(const double* d_xs, const double* d_us, int diff, double* d_costs) override;
+  void problem_rollout(const double* d_us, double* d_xs) override {
+    ensure_tmp();
+    to_soa(d_us, tmp_us, tmp_us, nullptr, 0, c.T * U);
+    tpp_rollout_kernel<M><<<nblocks(), 64, 0, stream>>>(c, tmp_us, tmp_xs);
+    ++last_launches;
+    to_user(d_xs, tmp_xs, tmp_xs, nullptr, 0, (c.T + 1) * N, 0, c.B);
+  }
+  void problem_quasi_static(const double*, double*) override {
+    throw Unsupported("quasiStatic is not implemented for this model family");
+  }
+  FieldInfo data_info(const std::string& name) override {
+    const int T = c.T;
+    if (name == "cost") return {1, T + 1};
+    if (name == "xnext") return {N, T + 1};
+    if (name == "Fx") return {N * N, T + 1};
+    if (name == "Fu") return {N * U, T + 1};
+    if (name == "Lx") return {N, T + 1};
+    if (name == "Lu") return {U, T + 1};
+    if (name == "Lxx") return {N * N, T + 1};
+    if (name == "Lxu") return {N * U, T + 1};
+    if (name == "Luu") return {U * U, T + 1};
+    throw NotFound("unknown data field " + name);
+  }
+  void export_data(const std::string& name, int b, int t, double* d_out) override {
+    static const char* names[9] = {"cost", "xnext", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu"};
+    FieldInfo fi = data_info(name);
+    for (int i = 0; i < 9; ++i)
+      if (name == names[i]) {
+        if (!node_data[i]) throw InvalidArg("node data not computed yet: call calc / calcDiff first");
+        CGX_CUDA(cudaMemcpyAsync(d_out, node_data[i] + ((size_t)b * (c.T + 1) + t) * fi.size,
+                                 fi.size * sizeof(double), cudaMemcpyDeviceToDevice, stream));
+      }
+  }
+};
+
+__global__ void tpp_scalars_kernel(TppCtx c, double* out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= c.B) return;
+  const int Bp = c.Bp;
+  double* o = out + (size_t)b * 17;
+  o[0] = TPP_S(S_COST);
+  o[1] = TPP_S(S_STOP);
+  o[2] = TPP_S(S_D0);
+  o[3] = TPP_S(S_D1);
+  o[4] = TPP_S(S_XREG);
+  o[5] = TPP_S(S_UREG);
+  o[6] = TPP_S(S_STEP);
+  o[7] = TPP_S(S_DV);
+  o[8] = TPP_S(S_DVEXP);
+  o[9] = TPP_I(I_ITER);
+  o[10] = TPP_I(I_FEAS);
+  o[11] = TPP_I(I_CONVERGED);
+  o[12] = TPP_I(I_NREC);
+  o[13] = TPP_S(S_COST_TRY);
+  o[14] = TPP_I(I_WASFEAS);
+  o[15] = TPP_I(I_NBWD);
+  o[16] = TPP_I(I_NFWD);
+}
+__global__ void tpp_setreg_kernel(TppCtx c, double xreg, double ureg, int set_x, int set_u) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= c.B) return;
+  const int Bp = c.Bp;
+  if (set_x) TPP_S(S_XREG) = xreg;
+  if (set_u) TPP_S(S_UREG) = ureg;
+}
+__global__ void tpp_trace_kernel(TppCtx c, int b, double* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= c.trace_cap * NTRACE) return;
+  out[i] = c.trace[(size_t)i * c.Bp + b];
+}
+__global__ void tpp_cost_sum_kernel(int B, int T, const double* node_cost, double* costs) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  double s = 0.;
+  for (int t = 0; t <= T; ++t) s += node_cost[(size_t)b * (T + 1) + t];  // shooting.hxx:155-159
+  costs[b] = s;
+}
+
+template <class M>
+void TppBackend<M>::export_scalars(double* d_out) {
+  tpp_scalars_kernel<<<nblocks(), 64, 0, stream>>>(c, d_out);
+  ++last_launches;
+}
+template <class M>
+void TppBackend<M>::set_reg(double xreg, double ureg, bool set_x, bool set_u) {
+  tpp_setreg_kernel<<<nblocks(), 64, 0, stream>>>(c, xreg, ureg, set_x, set_u);
+}
+template <class M>
+void TppBackend<M>::export_trace(int b, double* d_out) {
+  if (!c.trace) throw InvalidArg("trace recording is not enabled (cgx_solver_enable_trace)");
+  tpp_trace_kernel<<<(c.trace_cap * NTRACE + 63) / 64, 64, 0, stream>>>(c, b, d_out);
+}
+template <class M>
+void TppBackend<M>::problem_calc(const double* d_xs, const double* d_us, int diff, double* d_costs) {
+  ensure_tmp();
+  const size_t nodes = (size_t)c.B * (c.T + 1);
+  const int sizes[9] = {1, N, N * N, N * U, N, U, N * N, N * U, U * U};
+  for (int i = 0; i < 9; ++i)
+    if (!node_data[i]) node_data[i] = alloc(nodes * sizes[i]);
+  to_soa(d_xs, tmp_xs, tmp_xs, nullptr, 0, (c.T + 1) * N);
+  to_soa(d_us, tmp_us, tmp_us, nullptr, 0, c.T * U);
+  tpp_node_data_kernel<M><<<dim3(nblocks(), c.T + 1), 64, 0, stream>>>(
+      c, tmp_xs, tmp_us, diff, node_data[0], node_data[1], node_data[2], node_data[3], node_data[4], node_data[5],
+      node_data[6], node_data[7], node_data[8]);
+  ++last_launches;
+  tpp_cost_sum_kernel<<<nblocks(), 64, 0, stream>>>(c.B, c.T, node_data[0], d_costs);
+  ++last_launches;
+}
+
+}  // namespace
+
+Backend* make_tpp_backend(const ProblemDesc* p, int solver_kind) {
+  if (p->kind == 1) {
+    if (p->nx != 3 || p->nu != 2) throw InvalidArg("Invalid argument: ActionModelUnicycle has nx = 3, nu = 2");
+    if (p->per_problem_params) throw Unsupported("unicycle: per-problem parameters are not supported");
+    if (p->nparams != 3) throw InvalidArg("Invalid argument: unicycle params = [dt, w_x, w_u]");
+    return new TppBackend<UnicycleModel>(p, solver_kind);
+  }
+  throw Unsupported("thread-per-problem backend: unsupported model kind");
+}
+
+}  // namespace cgx

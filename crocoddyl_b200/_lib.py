@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libcrocoddyl_b200.so")
+LIB_PATH = os.environ.get("CROCODDYL_B200_LIB", os.path.join(HERE, "lib", "libcrocoddyl_b200.so"))
 
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)

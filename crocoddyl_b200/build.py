@@ -12,6 +12,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libcrocoddyl_b200.so")
+# per-source extra flags. tpp_backend.cu: the thread-per-problem solve kernel must stay <= 128 registers so
+# that 65,536 problems are resident in ONE wave (8 blocks x 64 threads per SM; measured: 144 registers already falls back to two waves).
+EXTRA = {"tpp_backend.cu": ["-maxrregcount=128"]}
 SOURCES = ["capi.cu", "tpp_backend.cu", "cta_backend.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-Xcompiler", "-fvisibility=hidden"]
@@ -29,11 +32,15 @@ def _digest():
     return h.hexdigest()
 
 
-def build(force=False, quiet=False, jobs=None):
-    """Compile every CUDA source for sm_100a and link the C-ABI library. Returns the library path."""
+def build(force=False, quiet=False, variant=None, extra=None):
+    """Compile every CUDA source for sm_100a and link the C-ABI library. Returns the library path.
+    variant/extra: development knob — builds lib/libcrocoddyl_b200_<variant>.so with other per-source flags
+    (select it at run time with CROCODDYL_B200_LIB)."""
     os.makedirs(LIBDIR, exist_ok=True)
-    stamp = os.path.join(LIBDIR, "build.stamp")
-    dig = _digest()
+    LIB = os.path.join(LIBDIR, "libcrocoddyl_b200%s.so" % ("_" + variant if variant else ""))
+    EXTRA = dict(globals()["EXTRA"]) if extra is None else extra
+    stamp = os.path.join(LIBDIR, "build%s.stamp" % ("_" + variant if variant else ""))
+    dig = _digest() + repr(sorted(EXTRA.items()))
     if not force and os.path.exists(LIB) and os.path.exists(stamp) and open(stamp).read() == dig:
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
@@ -42,9 +49,9 @@ def build(force=False, quiet=False, jobs=None):
     objs = []
     procs = []
     for src in SOURCES:
-        obj = os.path.join(LIBDIR, src.replace(".cu", ".o"))
+        obj = os.path.join(LIBDIR, src.replace(".cu", "%s.o" % ("_" + variant if variant else "")))
         objs.append(obj)
-        cmd = [nvcc] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc] + NVCC_FLAGS + EXTRA.get(src, []) + ["-c", os.path.join(CSRC, src), "-o", obj]
         if not quiet:
             print(" ".join(cmd), flush=True)
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))

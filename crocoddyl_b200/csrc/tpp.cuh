@@ -129,12 +129,18 @@ struct UnicycleModel {
   }
 };
 
+#define TPP_BLOCK 64
+#ifdef TPP_NOINLINE
+#define TPP_SWEEP_ATTR __device__ __noinline__
+#else
+#define TPP_SWEEP_ATTR __device__ __forceinline__
+#endif
 #define TPP_AT(ptr, t, D, i) (ptr)[((size_t)(t) * (D) + (i)) * (size_t)Bp + b]
 
 // ---------------------------------------------------------------------------------------------
 // problem_->calc(xs_, us_) in the reference's summation order (shooting.hxx:133-161): returns total cost.
 template <class M>
-__device__ double tpp_calc_pass(const TppCtx& c, const M& m, int b, const double* __restrict__ xs,
+TPP_SWEEP_ATTR double tpp_calc_pass(const TppCtx& c, const M& m, int b, const double* __restrict__ xs,
                                 const double* __restrict__ us) {
   constexpr int NX = M::NX, NU = M::NU;
   const int Bp = c.Bp, T = c.T;
@@ -163,7 +169,7 @@ __device__ double tpp_calc_pass(const TppCtx& c, const M& m, int b, const double
 // because fs[t+1] = xnext(xs[t],us[t]) - xs[t+1] (ddp.cpp:160-171) needs node t's calc; the operations
 // and their order per node are unchanged.
 template <class M>
-__device__ int tpp_backward(const TppCtx& c, const M& m, int b, const double* __restrict__ xs,
+TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, const double* __restrict__ xs,
                             const double* __restrict__ us, bool recalc, bool is_feasible, bool was_feasible,
                             double xreg, double ureg, double& dg_out, double& dq_out, double& stop_out) {
   constexpr int N = M::NX, U = M::NU;
@@ -191,13 +197,25 @@ __device__ int tpp_backward(const TppCtx& c, const M& m, int b, const double* __
 #pragma unroll
   for (int i = 0; i < N * N; ++i) TPP_AT(c.Vxx, T, N * N, i) = Vxx[i];
 
+  // software prefetch: node t-1's (x,u) are requested before node t's dependent Riccati chain starts
+  double xq[N], uq[U];
+#pragma unroll
+  for (int i = 0; i < N; ++i) xq[i] = TPP_AT(xs, T - 1, N, i);
+#pragma unroll
+  for (int i = 0; i < U; ++i) uq[i] = TPP_AT(us, T - 1, U, i);
   for (int t = T - 1; t >= -1; --t) {
     double f[N];
     if (t >= 0) {
 #pragma unroll
-      for (int i = 0; i < N; ++i) x[i] = TPP_AT(xs, t, N, i);
+      for (int i = 0; i < N; ++i) x[i] = xq[i];
 #pragma unroll
-      for (int i = 0; i < U; ++i) u[i] = TPP_AT(us, t, U, i);
+      for (int i = 0; i < U; ++i) u[i] = uq[i];
+      if (t > 0) {
+#pragma unroll
+        for (int i = 0; i < N; ++i) xq[i] = TPP_AT(xs, t - 1, N, i);
+#pragma unroll
+        for (int i = 0; i < U; ++i) uq[i] = TPP_AT(us, t - 1, U, i);
+      }
       m.calcBoth(x, u, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);
     } else {
       // gap of node 0: fs[0] = diff(xs[0], x0) = x0 - xs[0]   (ddp.cpp:162)
@@ -460,7 +478,7 @@ __device__ int tpp_backward(const TppCtx& c, const M& m, int b, const double* __
 // dv = -sum_t fs_t^T Vxx_t (xs_t - xs_try_t) = sum_t w_t^T dx_t (fddp.cpp:107-124).
 // Returns 0, or 1 = "forward_error".
 template <class M>
-__device__ int tpp_forward(const TppCtx& c, const M& m, int b, const double* __restrict__ xs,
+TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, const double* __restrict__ xs,
                            const double* __restrict__ us, double* __restrict__ xs_try, double* __restrict__ us_try,
                            double alpha, bool is_feasible, double& cost_try_out, double& dv_out) {
   constexpr int N = M::NX, U = M::NU;
@@ -473,23 +491,61 @@ __device__ int tpp_forward(const TppCtx& c, const M& m, int b, const double* __r
   double xn[N], xt[N], dx[N], u[U];
 #pragma unroll
   for (int i = 0; i < N; ++i) xn[i] = c.x0[(size_t)i * Bp + b];
+  // software prefetch of node t+1's inputs (none of them depends on the rollout recursion)
+  double qx[N], qf[N], qw[N], qu[U], qk[U], qK[U * N];
+  auto fetch = [&](int t) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) qx[i] = TPP_AT(xs, t, N, i);
+    if (!closed) {
+#pragma unroll
+      for (int i = 0; i < N; ++i) qf[i] = TPP_AT(c.fs, t, N, i);
+    }
+    if (use_w) {
+#pragma unroll
+      for (int i = 0; i < N; ++i) qw[i] = TPP_AT(c.w, t, N, i);
+    }
+    if (t < T) {
+#pragma unroll
+      for (int i = 0; i < U; ++i) {
+        qu[i] = TPP_AT(us, t, U, i);
+        qk[i] = TPP_AT(c.k, t, U, i);
+      }
+#pragma unroll
+      for (int i = 0; i < U * N; ++i) qK[i] = TPP_AT(c.K, t, U * N, i);
+    }
+  };
+  fetch(0);
   for (int t = 0; t <= T; ++t) {
+    double cx[N], cw[N], cu[U], ck[U], cK[U * N];
     if (closed) {
 #pragma unroll
       for (int i = 0; i < N; ++i) xt[i] = xn[i];
     } else {
 #pragma unroll
-      for (int i = 0; i < N; ++i) xt[i] = xn[i] + TPP_AT(c.fs, t, N, i) * am1;  // integrate(xnext, fs*(a-1))
+      for (int i = 0; i < N; ++i) xt[i] = xn[i] + qf[i] * am1;  // integrate(xnext, fs*(a-1))
     }
 #pragma unroll
     for (int i = 0; i < N; ++i) {
-      dx[i] = xt[i] - TPP_AT(xs, t, N, i);
+      cx[i] = qx[i];
+      cw[i] = qw[i];
+    }
+#pragma unroll
+    for (int i = 0; i < U; ++i) {
+      cu[i] = qu[i];
+      ck[i] = qk[i];
+    }
+#pragma unroll
+    for (int i = 0; i < U * N; ++i) cK[i] = qK[i];
+    if (t < T) fetch(t + 1);
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      dx[i] = xt[i] - cx[i];
       TPP_AT(xs_try, t, N, i) = xt[i];
     }
     if (use_w) {
       double s = 0.;
 #pragma unroll
-      for (int i = 0; i < N; ++i) s += TPP_AT(c.w, t, N, i) * dx[i];
+      for (int i = 0; i < N; ++i) s += cw[i] * dx[i];
       dv += s;
     }
     if (t == T) break;
@@ -497,8 +553,8 @@ __device__ int tpp_forward(const TppCtx& c, const M& m, int b, const double* __r
     for (int i = 0; i < U; ++i) {
       double s = 0.;
 #pragma unroll
-      for (int j = 0; j < N; ++j) s += TPP_AT(c.K, t, U * N, i + U * j) * dx[j];
-      u[i] = TPP_AT(us, t, U, i) - TPP_AT(c.k, t, U, i) * alpha - s;
+      for (int j = 0; j < N; ++j) s += cK[i + U * j] * dx[j];
+      u[i] = cu[i] - ck[i] * alpha - s;
       TPP_AT(us_try, t, U, i) = u[i];
     }
     cost_try += m.calc(xt, u, xn);
@@ -536,7 +592,7 @@ __device__ inline bool accept_step(const SolverOpts& o, bool fddp, bool is_feasi
 // ---------------------------------------------------------------------------------------------
 // Whole SolverDDP::solve / SolverFDDP::solve loop for one problem per thread (ddp.cpp:41-118, fddp.cpp:19-105).
 template <class M>
-__global__ void __launch_bounds__(64) tpp_solve_kernel(TppCtx c, int maxiter, int is_feasible0, double reginit) {
+__global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, int is_feasible0, double reginit) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= c.B) return;
   const int Bp = c.Bp;
@@ -658,7 +714,7 @@ __global__ void __launch_bounds__(64) tpp_solve_kernel(TppCtx c, int maxiter, in
 // computeDirection(recalc) (ddp.cpp:120-125): calcDiff (calc + gaps, ddp.cpp:157-178; the step-wise API
 // always runs with iter_ == 0, so problem_->calc is evaluated) + backwardPass.
 template <class M>
-__global__ void __launch_bounds__(64) tpp_direction_kernel(TppCtx c, int recalc) {
+__global__ void __launch_bounds__(64) tpp_direction_kernel(const __grid_constant__ TppCtx c, int recalc) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= c.B) return;
   const int Bp = c.Bp;
@@ -684,7 +740,7 @@ __global__ void __launch_bounds__(64) tpp_direction_kernel(TppCtx c, int recalc)
 
 // tryStep(alpha) (ddp.cpp:127-130)
 template <class M>
-__global__ void __launch_bounds__(64) tpp_trystep_kernel(TppCtx c, double alpha) {
+__global__ void __launch_bounds__(64) tpp_trystep_kernel(const __grid_constant__ TppCtx c, double alpha) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= c.B) return;
   const int Bp = c.Bp;

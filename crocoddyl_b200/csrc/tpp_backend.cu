@@ -140,7 +140,7 @@ struct TppBackend : Backend {
   void solve(int maxiter, int is_feasible, double reginit) override {
     c.o = o;
     CGX_CUDA(cudaEventRecord(ev[1], stream));
-    tpp_solve_kernel<M><<<nblocks(), 64, 0, stream>>>(c, maxiter, is_feasible, reginit);
+    tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit);
     CGX_CUDA(cudaEventRecord(ev[2], stream));
     ++last_launches;
     CGX_CUDA(cudaGetLastError());

@@ -35,9 +35,11 @@ B_PER_GPU = 65536
 NX, NU = 3, 2
 METRIC = "fddp_ocp_solves_per_sec_T100"
 UNIT = "solves/s"
-# algorithmic HBM bytes per node of the lean storage policy (DESIGN.md "bytes per node")
-BYTES_BWD_NODE = 8 * (NX + NU + NX + NU * NX + NU + NX + NX * NX + NX)  # read xs,us ; write fs,K,k,Vx,Vxx,w
-BYTES_FWD_NODE = 8 * (NX + NU + NU * NX + NU + NX + NX + NX + NU)       # read xs,us,K,k,fs,w ; write xs_try,us_try
+# algorithmic HBM bytes per node of the lean storage policy (DESIGN.md "bytes per node"): useful doubles only,
+# not the sector padding of the record layout
+NL = NX * (NX + 1) // 2
+BYTES_BWD_NODE = 8 * (NX + NU + NX + NU * NX + NU + NX + NX + NL)  # read xs,us ; write fs,K,k,w,Vx,tril(Vxx)
+BYTES_FWD_NODE = 8 * (NX + NU + NU * NX + NU + NX + NX + NX + NU)  # read xs,us,K,k,fs,w ; write xs_try,us_try
 BYTES_CALC_NODE = 8 * (NX + NU)
 
 

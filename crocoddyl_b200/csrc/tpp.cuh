@@ -1,14 +1,22 @@
 // crocoddyl_b200 — thread-per-problem (TPP) DDP/FDDP core for tiny node models (nx <= ~4).
 //
 // One CUDA thread owns one OCP and runs the reference's whole solve() loop on the device
-// (per-problem state machine, no host round trip per iteration). All per-node arrays are stored
-// structure-of-arrays with the BATCH INDEX FASTEST: element i of node t of problem b of a field of
-// width D lives at  ptr[(t*D + i)*Bp + b]  so that the 32 lanes of a warp (32 problems at the same
-// node) touch 32 consecutive doubles = one fully used 256-byte line.
+// (per-problem state machine, no host round trip per iteration).
+//
+// HBM layout ("lane-sector" records): every per-node quantity of problem b lives in a small record made of
+// whole 32-byte sectors, records of consecutive problems are adjacent:
+//     rec(t, b) = base + (t*Bp + b) * R        (R = record size in doubles, a multiple of 4)
+//   XU[2] : { x[N], u[U], fs[N] }      candidate / trial (double-buffered, picked by I_CUR)
+//   KK    : { K[U*N] column-major, k[U] }
+//   V     : { w[N] = Vxx fs, Vx[N], lower triangle of Vxx (column-major) }
+//   Q     : { Qxx, Qxu, Quu, Qx, Qu }  only with full storage
+// A lane moves only whole sectors with 256-bit LDG/STG, so (i) a full warp reads/writes 32 adjacent sectors
+// (1 KB, coalesced) and (ii) a warp that diverged — each OCP has its own iteration count — still uses every
+// byte of every sector it touches. (ncu on the first batch-fastest SoA version: 2.6x DRAM traffic over the
+// algorithmic bytes at 9.9 active lanes per warp instruction; profiles/.)
 //
 // Node derivatives (Fx,Fu,L**) and the gaps are generated INSIDE the backward sweep from (xs,us);
-// they never touch HBM. The accepted trial becomes the candidate by flipping a per-problem buffer
-// index (I_CUR) instead of copying xs_try/us_try.
+// they never touch HBM. The accepted trial becomes the candidate by flipping I_CUR (no copy).
 //
 // Reference functions restated here (paths relative to the reference tree):
 //   SolverDDP::calcDiff/backwardPass/computeGains  src/core/solvers/ddp.cpp:157-253,298-310
@@ -22,29 +30,61 @@ namespace cgx {
 
 struct TppCtx {
   int B, Bp, T;
-  int fddp;        // 1 = SolverFDDP, 0 = SolverDDP
-  int full;        // keep Qxx,Qxu,Quu,Qx,Qu per node
-  double* xs[2];   // [T+1][NX][Bp] candidate / trial (selected by I_CUR)
-  double* us[2];   // [T][NU][Bp]
-  double* fs;      // [T+1][NX][Bp]
-  double* K;       // [T][NU*NX][Bp] column-major NU x NX
-  double* k;       // [T][NU][Bp]
-  double* Vx;      // [T+1][NX][Bp]
-  double* Vxx;     // [T+1][NX*NX][Bp]
-  double* w;       // [T+1][NX][Bp]   w_t = Vxx_t fs_t  (fddp.cpp:112-118,132-144 only use Vxx through it)
-  double* Qxx;     // full only
-  double* Qxu;
-  double* Quu;
-  double* Qx;
-  double* Qu;
-  double* x0;      // [NX][Bp]
-  double* scal;    // [S_NSLOTS][Bp]
-  int* iscal;      // [I_NSLOTS][Bp]
-  double* trace;   // [cap][NTRACE][Bp] or null
+  int fddp;       // 1 = SolverFDDP, 0 = SolverDDP
+  int full;       // keep Qxx,Qxu,Quu,Qx,Qu per node
+  double* xu[2];  // [T+1][Bp][R_XU]
+  double* kk;     // [T][Bp][R_KK]
+  double* v;      // [T+1][Bp][R_V]
+  double* q;      // [T][Bp][R_Q] (full only)
+  double* x0;     // [NX][Bp]
+  double* scal;   // [S_NSLOTS][Bp]
+  int* iscal;     // [I_NSLOTS][Bp]
+  double* trace;  // [cap][NTRACE][Bp] or null
   int trace_cap;
   const double* mparams;  // shared model parameters
   SolverOpts o;
 };
+
+__host__ __device__ constexpr int rup4(int n) { return (n + 3) / 4 * 4; }
+
+template <class M>
+struct TppLayout {
+  static constexpr int N = M::NX, U = M::NU;
+  static constexpr int NL = N * (N + 1) / 2;
+  static constexpr int XU_X = 0, XU_U = N, XU_F = N + U, R_XU = rup4(2 * N + U);
+  static constexpr int KK_K = 0, KK_k = U * N, R_KK = rup4(U * N + U);
+  static constexpr int V_W = 0, V_VX = N, V_VXX = 2 * N, R_V = rup4(2 * N + NL);
+  static constexpr int Q_XX = 0, Q_XU = N * N, Q_UU = Q_XU + N * U, Q_X = Q_UU + U * U, Q_U = Q_X + N,
+                       R_Q = rup4(Q_U + U);
+  // index of (i,j), i >= j, in the column-major packed lower triangle
+  __host__ __device__ static constexpr int low(int i, int j) { return j * N - j * (j - 1) / 2 + (i - j); }
+  __host__ __device__ static constexpr int sym(int i, int j) { return i >= j ? low(i, j) : low(j, i); }
+};
+
+// 256-bit sector moves (LDG.E.256 / STG.E.256 on sm_100a) and L2 prefetch
+__device__ __forceinline__ void ld_sector(const double* p, double* o) {
+  asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(o[0]), "=d"(o[1]), "=d"(o[2]), "=d"(o[3]) : "l"(p));
+}
+__device__ __forceinline__ void st_sector(double* p, const double* o) {
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(o[0]), "d"(o[1]), "d"(o[2]), "d"(o[3]) : "memory");
+}
+__device__ __forceinline__ void prefetch_l2(const double* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+// sectors [s0, s1) of a record
+template <int S0, int S1>
+__device__ __forceinline__ void ld_rec(const double* p, double* o) {
+#pragma unroll
+  for (int s = S0; s < S1; ++s) ld_sector(p + 4 * s, o + 4 * s);
+}
+template <int S0, int S1>
+__device__ __forceinline__ void st_rec(double* p, const double* o) {
+#pragma unroll
+  for (int s = S0; s < S1; ++s) st_sector(p + 4 * s, o + 4 * s);
+}
+template <int S0, int S1>
+__device__ __forceinline__ void pf_rec(const double* p) {
+#pragma unroll
+  for (int s = S0; s < S1; ++s) prefetch_l2(p + 4 * s);
+}
 
 // ---------------------------------------------------------------------------------------------
 // ActionModelUnicycle (reference: include/crocoddyl/core/actions/unicycle.hxx:13-73, unicycle.hpp:78-80)
@@ -135,29 +175,29 @@ struct UnicycleModel {
 #else
 #define TPP_SWEEP_ATTR __device__ __forceinline__
 #endif
-#define TPP_AT(ptr, t, D, i) (ptr)[((size_t)(t) * (D) + (i)) * (size_t)Bp + b]
+#define TPP_PF_DIST 3  // L2 prefetch distance in nodes (the register prefetch is one node ahead)
+#define TPP_REC(base, t, R) ((base) + ((size_t)(t) * (size_t)Bp + b) * (R))
 
 // ---------------------------------------------------------------------------------------------
 // problem_->calc(xs_, us_) in the reference's summation order (shooting.hxx:133-161): returns total cost.
 template <class M>
-TPP_SWEEP_ATTR double tpp_calc_pass(const TppCtx& c, const M& m, int b, const double* __restrict__ xs,
-                                const double* __restrict__ us) {
-  constexpr int NX = M::NX, NU = M::NU;
+TPP_SWEEP_ATTR double tpp_calc_pass(const TppCtx& c, const M& m, int b, const double* __restrict__ xu) {
+  typedef TppLayout<M> L;
+  constexpr int N = M::NX, U = M::NU, SXU = rup4(N + U) / 4;
   const int Bp = c.Bp, T = c.T;
   double cost = 0.;
-  double x[NX], u[NU], xn[NX];
+  double rq[4 * SXU], r[4 * SXU], xn[N], u0[U];
+  ld_rec<0, SXU>(TPP_REC(xu, 0, L::R_XU), rq);
   for (int t = 0; t < T; ++t) {
 #pragma unroll
-    for (int i = 0; i < NX; ++i) x[i] = TPP_AT(xs, t, NX, i);
-#pragma unroll
-    for (int i = 0; i < NU; ++i) u[i] = TPP_AT(us, t, NU, i);
-    cost += m.calc(x, u, xn);
+    for (int i = 0; i < 4 * SXU; ++i) r[i] = rq[i];
+    ld_rec<0, SXU>(TPP_REC(xu, t + 1, L::R_XU), rq);
+    if (t + TPP_PF_DIST <= T) pf_rec<0, SXU>(TPP_REC(xu, t + TPP_PF_DIST, L::R_XU));
+    cost += m.calc(r + L::XU_X, r + L::XU_U, xn);
   }
 #pragma unroll
-  for (int i = 0; i < NX; ++i) x[i] = TPP_AT(xs, T, NX, i);
-#pragma unroll
-  for (int i = 0; i < NU; ++i) u[i] = 0.;
-  cost += m.calc(x, u, xn);
+  for (int i = 0; i < U; ++i) u0[i] = 0.;
+  cost += m.calc(rq + L::XU_X, u0, xn);
   return cost;
 }
 
@@ -167,105 +207,106 @@ TPP_SWEEP_ATTR double tpp_calc_pass(const TppCtx& c, const M& m, int b, const do
 // Returns 0, or 1 = "backward_error" (LLT pivot <= 0, ddp.cpp:302-304; NaN/inf/>=1e30 in Vx/Vxx, :246-251).
 // The gap term of node t+1 (Vx += Vxx fs, ddp.cpp:189-191,242-244) is applied when node t is visited,
 // because fs[t+1] = xnext(xs[t],us[t]) - xs[t+1] (ddp.cpp:160-171) needs node t's calc; the operations
-// and their order per node are unchanged.
+// and their order per node are unchanged. Vxx is exactly symmetric after ddp.cpp:235, so only its lower
+// triangle is carried and stored.
 template <class M>
-TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, const double* __restrict__ xs,
-                            const double* __restrict__ us, bool recalc, bool is_feasible, bool was_feasible,
-                            double xreg, double ureg, double& dg_out, double& dq_out, double& stop_out) {
-  constexpr int N = M::NX, U = M::NU;
+TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, bool recalc, bool is_feasible,
+                                bool was_feasible, double xreg, double ureg, double& dg_out, double& dq_out,
+                                double& stop_out) {
+  typedef TppLayout<M> L;
+  constexpr int N = M::NX, U = M::NU, NL = L::NL;
+  constexpr int SR = L::R_XU / 4, SF = L::XU_F / 4, SXU = rup4(N + U) / 4;
   const int Bp = c.Bp, T = c.T;
   const bool fddp = c.fddp != 0;
   const bool full = c.full != 0;
+  double* xu = c.xu[cur];
   double dg = 0., dq = 0., stop = 0.;
   const bool has_xreg = !isnan(xreg), has_ureg = !isnan(ureg);  // ddp.cpp:185,216,226,237
-  double Vxx[N * N], Vx[N], xp[N];
+  double Vl[NL], Vx[N];
   double Fx[N * N], Fu[N * U], Lx[N], Lu[U], Lxx[N * N], Lxu[N * U], Luu[U * U], xn[N];
-  double x[N], u[U];
+  double rp[L::R_XU], r[L::R_XU], rq[L::R_XU];
   // terminal node (ddp.cpp:181-187): u = unone_ = 0 (action-base.hxx:27-37)
+  ld_rec<0, SR>(TPP_REC(xu, T, L::R_XU), rp);
+  ld_rec<0, SR>(TPP_REC(xu, T - 1, L::R_XU), rq);
+  {
+    double u0[U];
 #pragma unroll
-  for (int i = 0; i < N; ++i) xp[i] = TPP_AT(xs, T, N, i);
-#pragma unroll
-  for (int i = 0; i < U; ++i) u[i] = 0.;
-  m.calcBoth(xp, u, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);
-#pragma unroll
-  for (int i = 0; i < N * N; ++i) Vxx[i] = Lxx[i];
-#pragma unroll
-  for (int i = 0; i < N; ++i) {
-    Vx[i] = Lx[i];
-    if (has_xreg) Vxx[i + N * i] += xreg;
+    for (int i = 0; i < U; ++i) u0[i] = 0.;
+    m.calcBoth(rp + L::XU_X, u0, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);
   }
 #pragma unroll
-  for (int i = 0; i < N * N; ++i) TPP_AT(c.Vxx, T, N * N, i) = Vxx[i];
+  for (int j = 0; j < N; ++j)
+#pragma unroll
+    for (int i = j; i < N; ++i) Vl[L::low(i, j)] = Lxx[i + N * j] + ((i == j && has_xreg) ? xreg : 0.);
+#pragma unroll
+  for (int i = 0; i < N; ++i) Vx[i] = Lx[i];
 
-  // software prefetch: node t-1's (x,u) are requested before node t's dependent Riccati chain starts
-  double xq[N], uq[U];
-#pragma unroll
-  for (int i = 0; i < N; ++i) xq[i] = TPP_AT(xs, T - 1, N, i);
-#pragma unroll
-  for (int i = 0; i < U; ++i) uq[i] = TPP_AT(us, T - 1, U, i);
   for (int t = T - 1; t >= -1; --t) {
-    double f[N];
     if (t >= 0) {
 #pragma unroll
-      for (int i = 0; i < N; ++i) x[i] = xq[i];
-#pragma unroll
-      for (int i = 0; i < U; ++i) u[i] = uq[i];
+      for (int i = 0; i < L::R_XU; ++i) r[i] = rq[i];
+      // software prefetch: node t-1's record is requested before node t's dependent Riccati chain starts,
+      // node t-1-TPP_PF_DIST's record is pulled into L2
       if (t > 0) {
-#pragma unroll
-        for (int i = 0; i < N; ++i) xq[i] = TPP_AT(xs, t - 1, N, i);
-#pragma unroll
-        for (int i = 0; i < U; ++i) uq[i] = TPP_AT(us, t - 1, U, i);
+        if (recalc)
+          ld_rec<0, SXU>(TPP_REC(xu, t - 1, L::R_XU), rq);
+        else
+          ld_rec<0, SR>(TPP_REC(xu, t - 1, L::R_XU), rq);
       }
-      m.calcBoth(x, u, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);
+      if (t > TPP_PF_DIST) pf_rec<0, SR>(TPP_REC(xu, t - 1 - TPP_PF_DIST, L::R_XU));
+      m.calcBoth(r + L::XU_X, r + L::XU_U, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);
     } else {
       // gap of node 0: fs[0] = diff(xs[0], x0) = x0 - xs[0]   (ddp.cpp:162)
 #pragma unroll
       for (int i = 0; i < N; ++i) xn[i] = c.x0[(size_t)i * Bp + b];
     }
-    // ---- finish node t+1: gap term, Vx store ----
+    // ---- finish node t+1: gap term, V record ----
+    double vrec[L::R_V];
+#pragma unroll
+    for (int i = 0; i < L::R_V; ++i) vrec[i] = 0.;
     if (!is_feasible) {
       if (recalc) {
 #pragma unroll
-        for (int i = 0; i < N; ++i) {
-          f[i] = xn[i] - xp[i];
-          TPP_AT(c.fs, t + 1, N, i) = f[i];
-        }
-      } else {
+        for (int i = 0; i < N; ++i) rp[L::XU_F + i] = xn[i] - rp[L::XU_X + i];
 #pragma unroll
-        for (int i = 0; i < N; ++i) f[i] = TPP_AT(c.fs, t + 1, N, i);
+        for (int i = L::XU_F + N; i < L::R_XU; ++i) rp[i] = 0.;
+        st_rec<SF, SR>(TPP_REC(xu, t + 1, L::R_XU), rp);
       }
-      double wv[N];
+      const double* f = rp + L::XU_F;
 #pragma unroll
       for (int i = 0; i < N; ++i) {
         double s = 0.;
 #pragma unroll
-        for (int j = 0; j < N; ++j) s += Vxx[i + N * j] * f[j];
-        wv[i] = s;
+        for (int j = 0; j < N; ++j) s += Vl[L::sym(i, j)] * f[j];
+        vrec[L::V_W + i] = s;
         Vx[i] += s;
-        TPP_AT(c.w, t + 1, N, i) = s;
       }
       if (fddp) {  // updateExpectedImprovement gap terms (fddp.cpp:131-135,141-145)
         double a = 0., q = 0.;
 #pragma unroll
         for (int i = 0; i < N; ++i) {
           a += Vx[i] * f[i];
-          q += f[i] * wv[i];
+          q += f[i] * vrec[L::V_W + i];
         }
         dg -= a;
         dq += q;
       }
     } else if (recalc && !was_feasible) {
 #pragma unroll
-      for (int i = 0; i < N; ++i) TPP_AT(c.fs, t + 1, N, i) = 0.;  // ddp.cpp:172-176
+      for (int i = L::XU_F; i < L::R_XU; ++i) rp[i] = 0.;  // ddp.cpp:172-176
+      st_rec<SF, SR>(TPP_REC(xu, t + 1, L::R_XU), rp);
     }
     {
       double nrm = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) {
-        TPP_AT(c.Vx, t + 1, N, i) = Vx[i];
+        vrec[L::V_VX + i] = Vx[i];
         const double v = fabs(Vx[i]);
         if (!(v <= nrm)) nrm = v;
       }
+#pragma unroll
+      for (int i = 0; i < NL; ++i) vrec[L::V_VXX + i] = Vl[i];
+      st_rec<0, L::R_V / 4>(TPP_REC(c.v, t + 1, L::R_V), vrec);
       if (t + 1 < T && raise_if_nan(nrm)) return 1;  // ddp.cpp:246-248
     }
     if (t < 0) break;
@@ -278,7 +319,7 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, const double
       for (int i = 0; i < N; ++i) {
         double s = 0.;
 #pragma unroll
-        for (int kk = 0; kk < N; ++kk) s += Fx[kk + N * i] * Vxx[kk + N * j];
+        for (int kk = 0; kk < N; ++kk) s += Fx[kk + N * i] * Vl[L::sym(kk, j)];
         A[i + N * j] = s;
       }
     double Qxx[N * N], Qx[N], Qxu[N * U], Quu[U * U], Qu[U], G[U * N];  // G = FuTVxx_p = Fu^T Vxx'
@@ -304,7 +345,7 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, const double
       for (int i = 0; i < U; ++i) {
         double s = 0.;
 #pragma unroll
-        for (int kk = 0; kk < N; ++kk) s += Fu[kk + N * i] * Vxx[kk + N * j];
+        for (int kk = 0; kk < N; ++kk) s += Fu[kk + N * i] * Vl[L::sym(kk, j)];
         G[i + U * j] = s;
       }
 #pragma unroll
@@ -334,54 +375,58 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, const double
       if (has_ureg) Quu[j + U * j] += ureg;
     }
     // computeGains (ddp.cpp:298-310): unblocked lower LLT, failure iff pivot <= 0
-    double L[U * U];
+    double Lc[U * U];
 #pragma unroll
-    for (int i = 0; i < U * U; ++i) L[i] = Quu[i];
+    for (int i = 0; i < U * U; ++i) Lc[i] = Quu[i];
     bool fail = false;
 #pragma unroll
     for (int kk = 0; kk < U; ++kk) {
-      double p = L[kk + U * kk];
+      double p = Lc[kk + U * kk];
 #pragma unroll
-      for (int j = 0; j < kk; ++j) p -= L[kk + U * j] * L[kk + U * j];
+      for (int j = 0; j < kk; ++j) p -= Lc[kk + U * j] * Lc[kk + U * j];
       if (p <= 0.) fail = true;
       p = sqrt(p);
-      L[kk + U * kk] = p;
+      Lc[kk + U * kk] = p;
 #pragma unroll
       for (int i = kk + 1; i < U; ++i) {
-        double s = L[i + U * kk];
+        double s = Lc[i + U * kk];
 #pragma unroll
-        for (int j = 0; j < kk; ++j) s -= L[i + U * j] * L[kk + U * j];
-        L[i + U * kk] = s / p;
+        for (int j = 0; j < kk; ++j) s -= Lc[i + U * j] * Lc[kk + U * j];
+        Lc[i + U * kk] = s / p;
       }
     }
     if (fail) return 1;
-    double Kg[U * N], kg[U];
+    double kkrec[L::R_KK];
+#pragma unroll
+    for (int i = 0; i < L::R_KK; ++i) kkrec[i] = 0.;
+    double* Kg = kkrec + L::KK_K;
+    double* kg = kkrec + L::KK_k;
     // K = Quu^-1 Qxu^T  (columns of K), k = Quu^-1 Qu
 #pragma unroll
     for (int col = 0; col <= N; ++col) {
-      double r[U];
+      double rr[U];
 #pragma unroll
-      for (int i = 0; i < U; ++i) r[i] = (col < N) ? Qxu[col + N * i] : Qu[i];
+      for (int i = 0; i < U; ++i) rr[i] = (col < N) ? Qxu[(col < N ? col : 0) + N * i] : Qu[i];
 #pragma unroll
       for (int i = 0; i < U; ++i) {
-        double s = r[i];
+        double s = rr[i];
 #pragma unroll
-        for (int j = 0; j < i; ++j) s -= L[i + U * j] * r[j];
-        r[i] = s / L[i + U * i];
+        for (int j = 0; j < i; ++j) s -= Lc[i + U * j] * rr[j];
+        rr[i] = s / Lc[i + U * i];
       }
 #pragma unroll
       for (int i = U - 1; i >= 0; --i) {
-        double s = r[i];
+        double s = rr[i];
 #pragma unroll
-        for (int j = i + 1; j < U; ++j) s -= L[j + U * i] * r[j];
-        r[i] = s / L[i + U * i];
+        for (int j = i + 1; j < U; ++j) s -= Lc[j + U * i] * rr[j];
+        rr[i] = s / Lc[i + U * i];
       }
 #pragma unroll
       for (int i = 0; i < U; ++i) {
         if (col < N)
-          Kg[i + U * col] = r[i];
+          Kg[i + U * (col < N ? col : 0)] = rr[i];
         else
-          kg[i] = r[i];
+          kg[i] = rr[i];
       }
     }
     double Quuk[U];
@@ -405,22 +450,22 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, const double
       dq -= q;
       stop += st;
     }
-    // stores
-#pragma unroll
-    for (int i = 0; i < U * N; ++i) TPP_AT(c.K, t, U * N, i) = Kg[i];
-#pragma unroll
-    for (int i = 0; i < U; ++i) TPP_AT(c.k, t, U, i) = kg[i];
+    st_rec<0, L::R_KK / 4>(TPP_REC(c.kk, t, L::R_KK), kkrec);
     if (full) {
+      double qrec[L::R_Q];
 #pragma unroll
-      for (int i = 0; i < N * N; ++i) TPP_AT(c.Qxx, t, N * N, i) = Qxx[i];
+      for (int i = 0; i < L::R_Q; ++i) qrec[i] = 0.;
 #pragma unroll
-      for (int i = 0; i < N * U; ++i) TPP_AT(c.Qxu, t, N * U, i) = Qxu[i];
+      for (int i = 0; i < N * N; ++i) qrec[L::Q_XX + i] = Qxx[i];
 #pragma unroll
-      for (int i = 0; i < U * U; ++i) TPP_AT(c.Quu, t, U * U, i) = Quu[i];
+      for (int i = 0; i < N * U; ++i) qrec[L::Q_XU + i] = Qxu[i];
 #pragma unroll
-      for (int i = 0; i < N; ++i) TPP_AT(c.Qx, t, N, i) = Qx[i];
+      for (int i = 0; i < U * U; ++i) qrec[L::Q_UU + i] = Quu[i];
 #pragma unroll
-      for (int i = 0; i < U; ++i) TPP_AT(c.Qu, t, U, i) = Qu[i];
+      for (int i = 0; i < N; ++i) qrec[L::Q_X + i] = Qx[i];
+#pragma unroll
+      for (int i = 0; i < U; ++i) qrec[L::Q_U + i] = Qu[i];
+      st_rec<0, L::R_Q / 4>(TPP_REC(c.q, t, L::R_Q), qrec);
     }
     // Vx = Qx + K^T Quuk - 2 K^T Qu ; Vxx = Qxx - Qxu K   (ddp.cpp:223-233)
 #pragma unroll
@@ -454,17 +499,16 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, const double
 #pragma unroll
     for (int j = 0; j < N; ++j)
 #pragma unroll
-      for (int i = 0; i < N; ++i) {
+      for (int i = j; i < N; ++i) {
         double v = 0.5 * (Vr[i + N * j] + Vr[j + N * i]);  // ddp.cpp:235
         if (i == j && has_xreg) v += xreg;                 // ddp.cpp:237-239
-        Vxx[i + N * j] = v;
-        TPP_AT(c.Vxx, t, N * N, i + N * j) = v;
+        Vl[L::low(i, j)] = v;
         const double av = fabs(v);
         if (!(av <= nrm)) nrm = av;
       }
     if (raise_if_nan(nrm)) return 1;  // ddp.cpp:249-251
 #pragma unroll
-    for (int i = 0; i < N; ++i) xp[i] = x[i];
+    for (int i = 0; i < L::R_XU; ++i) rp[i] = r[i];
   }
   dg_out = dg;
   dq_out = dq;
@@ -476,71 +520,62 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, const double
 // SolverFDDP::forwardPass (fddp.cpp:149-225) / SolverDDP::forwardPass (ddp.cpp:255-296, == the closed
 // branch with xs_try[0] = x0) fused with SolverFDDP::expectedImprovement's gap reduction
 // dv = -sum_t fs_t^T Vxx_t (xs_t - xs_try_t) = sum_t w_t^T dx_t (fddp.cpp:107-124).
-// Returns 0, or 1 = "forward_error".
+// Reads the candidate records XU[cur], writes the trial records XU[cur^1]. Returns 0, or 1 = "forward_error".
 template <class M>
-TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, const double* __restrict__ xs,
-                           const double* __restrict__ us, double* __restrict__ xs_try, double* __restrict__ us_try,
-                           double alpha, bool is_feasible, double& cost_try_out, double& dv_out) {
+TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, int cur, double alpha, bool is_feasible,
+                               double& cost_try_out, double& dv_out) {
+  typedef TppLayout<M> L;
   constexpr int N = M::NX, U = M::NU;
+  constexpr int SR = L::R_XU / 4, SK = L::R_KK / 4, SW = rup4(N) / 4;
   const int Bp = c.Bp, T = c.T;
   const bool fddp = c.fddp != 0;
   const bool closed = !fddp || is_feasible || (alpha == 1.);
   const bool use_w = fddp && !is_feasible;
   const double am1 = alpha - 1.;
+  const double* __restrict__ xu = c.xu[cur];
+  double* __restrict__ xt_ = c.xu[cur ^ 1];
   double cost_try = 0., dv = 0.;
-  double xn[N], xt[N], dx[N], u[U];
+  double xn[N], xt[N], dx[N];
+  // software prefetch of node t+1's inputs (none of them depends on the rollout recursion)
+  double qa[L::R_XU], qk[L::R_KK], qw[4 * SW];
+#pragma unroll
+  for (int i = 0; i < 4 * SW; ++i) qw[i] = 0.;
+  auto fetch = [&](int t) {
+    ld_rec<0, SR>(TPP_REC(xu, t, L::R_XU), qa);
+    if (use_w) ld_rec<0, SW>(TPP_REC(c.v, t, L::R_V), qw);
+    if (t < T) ld_rec<0, SK>(TPP_REC(c.kk, t, L::R_KK), qk);
+  };
+  auto prefetch = [&](int t) {
+    pf_rec<0, SR>(TPP_REC(xu, t, L::R_XU));
+    if (use_w) pf_rec<0, SW>(TPP_REC(c.v, t, L::R_V));
+    if (t < T) pf_rec<0, SK>(TPP_REC(c.kk, t, L::R_KK));
+  };
 #pragma unroll
   for (int i = 0; i < N; ++i) xn[i] = c.x0[(size_t)i * Bp + b];
-  // software prefetch of node t+1's inputs (none of them depends on the rollout recursion)
-  double qx[N], qf[N], qw[N], qu[U], qk[U], qK[U * N];
-  auto fetch = [&](int t) {
-#pragma unroll
-    for (int i = 0; i < N; ++i) qx[i] = TPP_AT(xs, t, N, i);
-    if (!closed) {
-#pragma unroll
-      for (int i = 0; i < N; ++i) qf[i] = TPP_AT(c.fs, t, N, i);
-    }
-    if (use_w) {
-#pragma unroll
-      for (int i = 0; i < N; ++i) qw[i] = TPP_AT(c.w, t, N, i);
-    }
-    if (t < T) {
-#pragma unroll
-      for (int i = 0; i < U; ++i) {
-        qu[i] = TPP_AT(us, t, U, i);
-        qk[i] = TPP_AT(c.k, t, U, i);
-      }
-#pragma unroll
-      for (int i = 0; i < U * N; ++i) qK[i] = TPP_AT(c.K, t, U * N, i);
-    }
-  };
   fetch(0);
   for (int t = 0; t <= T; ++t) {
-    double cx[N], cw[N], cu[U], ck[U], cK[U * N];
+    double ca[L::R_XU], ck[L::R_KK], cw[N], o[L::R_XU];
+#pragma unroll
+    for (int i = 0; i < L::R_XU; ++i) ca[i] = qa[i];
+#pragma unroll
+    for (int i = 0; i < L::R_KK; ++i) ck[i] = qk[i];
+#pragma unroll
+    for (int i = 0; i < N; ++i) cw[i] = qw[L::V_W + i];
+    if (t < T) fetch(t + 1);
+    if (t + TPP_PF_DIST <= T) prefetch(t + TPP_PF_DIST);
     if (closed) {
 #pragma unroll
       for (int i = 0; i < N; ++i) xt[i] = xn[i];
     } else {
 #pragma unroll
-      for (int i = 0; i < N; ++i) xt[i] = xn[i] + qf[i] * am1;  // integrate(xnext, fs*(a-1))
+      for (int i = 0; i < N; ++i) xt[i] = xn[i] + ca[L::XU_F + i] * am1;  // integrate(xnext, fs*(a-1))
     }
+#pragma unroll
+    for (int i = 0; i < L::R_XU; ++i) o[i] = 0.;
 #pragma unroll
     for (int i = 0; i < N; ++i) {
-      cx[i] = qx[i];
-      cw[i] = qw[i];
-    }
-#pragma unroll
-    for (int i = 0; i < U; ++i) {
-      cu[i] = qu[i];
-      ck[i] = qk[i];
-    }
-#pragma unroll
-    for (int i = 0; i < U * N; ++i) cK[i] = qK[i];
-    if (t < T) fetch(t + 1);
-#pragma unroll
-    for (int i = 0; i < N; ++i) {
-      dx[i] = xt[i] - cx[i];
-      TPP_AT(xs_try, t, N, i) = xt[i];
+      dx[i] = xt[i] - ca[L::XU_X + i];
+      o[L::XU_X + i] = xt[i];
     }
     if (use_w) {
       double s = 0.;
@@ -548,15 +583,19 @@ TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, const double*
       for (int i = 0; i < N; ++i) s += cw[i] * dx[i];
       dv += s;
     }
-    if (t == T) break;
+    if (t == T) {
+      st_rec<0, SR>(TPP_REC(xt_, t, L::R_XU), o);
+      break;
+    }
+    double* u = o + L::XU_U;
 #pragma unroll
     for (int i = 0; i < U; ++i) {
       double s = 0.;
 #pragma unroll
-      for (int j = 0; j < N; ++j) s += cK[i + U * j] * dx[j];
-      u[i] = cu[i] - ck[i] * alpha - s;
-      TPP_AT(us_try, t, U, i) = u[i];
+      for (int j = 0; j < N; ++j) s += ck[L::KK_K + i + U * j] * dx[j];
+      u[i] = ca[L::XU_U + i] - ck[L::KK_k + i] * alpha - s;
     }
+    st_rec<0, SR>(TPP_REC(xt_, t, L::R_XU), o);
     cost_try += m.calc(xt, u, xn);
     double nrm = 0.;
 #pragma unroll
@@ -566,9 +605,12 @@ TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, const double*
     }
     if (raise_if_nan(cost_try) || raise_if_nan(nrm)) return 1;
   }
+  {
+    double u0[U];
 #pragma unroll
-  for (int i = 0; i < U; ++i) u[i] = 0.;
-  cost_try += m.calc(xt, u, xn);
+    for (int i = 0; i < U; ++i) u0[i] = 0.;
+    cost_try += m.calc(xt, u0, xn);
+  }
   if (raise_if_nan(cost_try)) return 1;
   cost_try_out = cost_try;
   dv_out = dv;
@@ -599,7 +641,7 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
   const bool fddp = c.fddp != 0;
   M m;
   m.load(c.mparams);
-  int cur = TPP_I(I_CUR);
+  int cur = TPP_I(I_CUR), fsbuf = TPP_I(I_FSBUF);
   bool feas = is_feasible0 != 0, wasfeas = false;
   double xreg = isnan(reginit) ? c.o.regmin : reginit, ureg = xreg;
   double cost = TPP_S(S_COST), stop = TPP_S(S_STOP), d0 = TPP_S(S_D0), d1 = TPP_S(S_D1);
@@ -608,16 +650,15 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
   int nbwd = 0, nfwd = 0, nrec = 0, converged = 0, iter = 0;
   bool recalc = true, need_gaps = true, done = false;
   for (iter = 0; iter < maxiter && !done; ++iter) {
-    const double* xs = c.xs[cur];
-    const double* us = c.us[cur];
     int retries = 0;
     if (recalc && iter == 0) {  // ddp.cpp:158
-      cost = tpp_calc_pass(c, m, b, xs, us);
+      cost = tpp_calc_pass(c, m, b, c.xu[cur]);
       ++nfwd;
     }
     if (recalc) need_gaps = true;
     while (true) {  // computeDirection with regularisation retry (ddp.cpp:55-68)
-      const int st = tpp_backward(c, m, b, xs, us, need_gaps, feas, wasfeas, xreg, ureg, dg, dq, stop);
+      if (need_gaps) fsbuf = cur;
+      const int st = tpp_backward(c, m, b, cur, need_gaps, feas, wasfeas, xreg, ureg, dg, dq, stop);
       ++nbwd;
       if (st == 0) {
         need_gaps = false;
@@ -641,7 +682,7 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
     for (int a = 0; a < c.o.nalphas; ++a) {
       steplength = c.o.alphas[a];
       double dv = 0.;
-      const int st = tpp_forward(c, m, b, xs, us, c.xs[cur ^ 1], c.us[cur ^ 1], steplength, feas, cost_try, dv);
+      const int st = tpp_forward(c, m, b, cur, steplength, feas, cost_try, dv);
       ++nfwd;
       if (st) continue;
       dV = cost - cost_try;
@@ -704,6 +745,7 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
   TPP_I(I_WASFEAS) = wasfeas;
   TPP_I(I_CONVERGED) = converged;
   TPP_I(I_CUR) = cur;
+  TPP_I(I_FSBUF) = fsbuf;
   TPP_I(I_NREC) = nrec;
   TPP_I(I_NBWD) = nbwd;
   TPP_I(I_NFWD) = nfwd;
@@ -722,10 +764,12 @@ __global__ void __launch_bounds__(64) tpp_direction_kernel(const __grid_constant
   m.load(c.mparams);
   const int cur = TPP_I(I_CUR);
   const bool feas = TPP_I(I_FEAS) != 0, wasfeas = TPP_I(I_WASFEAS) != 0;
-  if (recalc) TPP_S(S_COST) = tpp_calc_pass(c, m, b, c.xs[cur], c.us[cur]);
+  if (recalc) {
+    TPP_S(S_COST) = tpp_calc_pass(c, m, b, c.xu[cur]);
+    TPP_I(I_FSBUF) = cur;
+  }
   double dg = 0., dq = 0., stop = 0.;
-  const int st = tpp_backward(c, m, b, c.xs[cur], c.us[cur], recalc != 0, feas, wasfeas, TPP_S(S_XREG),
-                              TPP_S(S_UREG), dg, dq, stop);
+  const int st = tpp_backward(c, m, b, cur, recalc != 0, feas, wasfeas, TPP_S(S_XREG), TPP_S(S_UREG), dg, dq, stop);
   TPP_I(I_BSTATUS) = st;
   if (st == 0) {
     TPP_S(S_DG) = dg;
@@ -749,7 +793,7 @@ __global__ void __launch_bounds__(64) tpp_trystep_kernel(const __grid_constant__
   const int cur = TPP_I(I_CUR);
   const bool feas = TPP_I(I_FEAS) != 0;
   double cost_try = 0., dv = 0.;
-  const int st = tpp_forward(c, m, b, c.xs[cur], c.us[cur], c.xs[cur ^ 1], c.us[cur ^ 1], alpha, feas, cost_try, dv);
+  const int st = tpp_forward(c, m, b, cur, alpha, feas, cost_try, dv);
   TPP_I(I_FSTATUS) = st;
   if (st == 0) {
     TPP_S(S_COST_TRY) = cost_try;
@@ -763,25 +807,25 @@ __global__ void __launch_bounds__(64) tpp_trystep_kernel(const __grid_constant__
   }
 }
 
-// ShootingProblem::calc / calcDiff for one (problem, node) per thread, results in the host ("user") layout
-// [B][T+1][size] (shooting.hxx:133-195). xs/us in SoA layout.
+// ShootingProblem::calc / calcDiff for one (problem, node) per thread; inputs and results in the host ("user")
+// layout [B][T+1][size] (shooting.hxx:133-195).
 template <class M>
 __global__ void tpp_node_data_kernel(TppCtx c, const double* __restrict__ xs, const double* __restrict__ us,
                                      int diff, double* cost, double* xnext, double* Fx, double* Fu, double* Lx,
                                      double* Lu, double* Lxx, double* Lxu, double* Luu) {
   constexpr int N = M::NX, U = M::NU;
-  const int Bp = c.Bp, T = c.T;
+  const int T = c.T;
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   const int t = blockIdx.y;
   if (b >= c.B) return;
   M m;
   m.load(c.mparams);
   double x[N], u[U], xn[N], fx[N * N], fu[N * U], lx[N], lu[U], lxx[N * N], lxu[N * U], luu[U * U];
-#pragma unroll
-  for (int i = 0; i < N; ++i) x[i] = TPP_AT(xs, t, N, i);
-#pragma unroll
-  for (int i = 0; i < U; ++i) u[i] = (t < T) ? TPP_AT(us, t < T ? t : 0, U, i) : 0.;
   const size_t node = (size_t)b * (T + 1) + t;
+#pragma unroll
+  for (int i = 0; i < N; ++i) x[i] = xs[node * N + i];
+#pragma unroll
+  for (int i = 0; i < U; ++i) u[i] = (t < T) ? us[((size_t)b * T + (t < T ? t : 0)) * U + i] : 0.;
   if (!diff) {
     cost[node] = m.calc(x, u, xn);
     for (int i = 0; i < N; ++i) xnext[node * N + i] = xn[i];
@@ -797,7 +841,7 @@ __global__ void tpp_node_data_kernel(TppCtx c, const double* __restrict__ xs, co
   }
 }
 
-// ShootingProblem::rollout (shooting.hxx:198-223); xs/us SoA
+// ShootingProblem::rollout (shooting.hxx:198-223); us/xs in the user layout
 template <class M>
 __global__ void tpp_rollout_kernel(TppCtx c, const double* __restrict__ us, double* __restrict__ xs) {
   constexpr int N = M::NX, U = M::NU;
@@ -811,57 +855,45 @@ __global__ void tpp_rollout_kernel(TppCtx c, const double* __restrict__ us, doub
   for (int i = 0; i < N; ++i) x[i] = c.x0[(size_t)i * Bp + b];
   for (int t = 0; t < T; ++t) {
 #pragma unroll
-    for (int i = 0; i < N; ++i) TPP_AT(xs, t, N, i) = x[i];
+    for (int i = 0; i < N; ++i) xs[((size_t)b * (T + 1) + t) * N + i] = x[i];
 #pragma unroll
-    for (int i = 0; i < U; ++i) u[i] = TPP_AT(us, t, U, i);
+    for (int i = 0; i < U; ++i) u[i] = us[((size_t)b * T + t) * U + i];
     m.calc(x, u, xn);
 #pragma unroll
     for (int i = 0; i < N; ++i) x[i] = xn[i];
   }
 #pragma unroll
-  for (int i = 0; i < N; ++i) TPP_AT(xs, T, N, i) = x[i];
+  for (int i = 0; i < N; ++i) xs[((size_t)b * (T + 1) + T) * N + i] = x[i];
 }
 
 // ---------------------------------------------------------------------------------------------
-// Layout conversion between the host layout [B][W] (W = nt*D contiguous doubles per problem) and the
-// batch-fastest SoA [W][Bp], through a 32x33 shared-memory tile so both sides are coalesced.
-// to_soa != 0: user -> soa ; else soa -> user. Problems b0..b0+nb-1 (user buffer holds nb problems).
-// If cur != null, soa0/soa1 is picked per problem by cur[b] ^ flip (double-buffered candidate/trial).
-__global__ void tpp_transpose_kernel(double* user, double* soa0, double* soa1, const int* cur, int flip, int W, int Bp,
-                                     int b0, int nb, int to_soa) {
-  __shared__ double tile[32][33];
-  const int bx = blockIdx.x * 32;  // problem offset within the range
-  const int wy = blockIdx.y * 32;  // element offset
-  const int tx = threadIdx.x, ty = threadIdx.y;  // 32 x 8
-  if (to_soa) {
-    for (int r = ty; r < 32; r += 8) {
-      const int bl = bx + r, wi = wy + tx;
-      if (bl < nb && wi < W) tile[r][tx] = user[(size_t)bl * W + wi];
-    }
-    __syncthreads();
-    for (int r = ty; r < 32; r += 8) {
-      const int wi = wy + r, bl = bx + tx;
-      if (bl < nb && wi < W) {
-        const int b = b0 + bl;
-        double* dst = (cur && ((cur[b] ^ flip) & 1)) ? soa1 : soa0;
-        dst[(size_t)wi * Bp + b] = tile[tx][r];
-      }
-    }
+// Layout conversion between the host layout [nb][nt][size] and the record arrays. One thread per
+// (problem, node): record side coalesced across the warp, host side strided (one pass per solve; small next to
+// the solve itself). sel (may be null) picks base0/base1 per problem: buffer = (sel[b] ^ flip) & 1.
+struct TppFieldMap {
+  int R, size, nt;
+  int off[16];
+};
+__global__ void tpp_gather_kernel(double* user, double* base0, double* base1, const int* sel, int flip,
+                                  TppFieldMap fm, int Bp, int b0, int nb, int to_rec) {
+  const int bl = blockIdx.x * blockDim.x + threadIdx.x;
+  const int t = blockIdx.y;
+  if (bl >= nb) return;
+  const int b = b0 + bl;
+  double* base = (sel && ((sel[b] ^ flip) & 1)) ? base1 : base0;
+  double* rec = base + ((size_t)t * Bp + b) * fm.R;
+  double* up = user + ((size_t)bl * fm.nt + t) * fm.size;
+  if (to_rec) {
+    for (int e = 0; e < fm.size; ++e) rec[fm.off[e]] = up[e];
   } else {
-    for (int r = ty; r < 32; r += 8) {
-      const int wi = wy + r, bl = bx + tx;
-      if (bl < nb && wi < W) {
-        const int b = b0 + bl;
-        const double* src = (cur && ((cur[b] ^ flip) & 1)) ? soa1 : soa0;
-        tile[tx][r] = src[(size_t)wi * Bp + b];
-      }
-    }
-    __syncthreads();
-    for (int r = ty; r < 32; r += 8) {
-      const int bl = bx + r, wi = wy + tx;
-      if (bl < nb && wi < W) user[(size_t)bl * W + wi] = tile[r][tx];
-    }
+    for (int e = 0; e < fm.size; ++e) up[e] = rec[fm.off[e]];
   }
+}
+// x0: host [B][N] -> [N][Bp]
+__global__ void tpp_x0_kernel(const double* user, double* x0, int N, int B, int Bp) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  for (int i = 0; i < N; ++i) x0[(size_t)i * Bp + b] = user[(size_t)b * N + i];
 }
 
 // setCandidate bookkeeping (solver-base.cpp:42-67) + reset of the step-wise state
@@ -874,6 +906,7 @@ __global__ void tpp_reset_kernel(TppCtx c, int is_feasible) {
   TPP_I(I_WASFEAS) = 0;
   TPP_I(I_CONVERGED) = 0;
   TPP_I(I_CUR) = 0;
+  TPP_I(I_FSBUF) = 0;
   TPP_I(I_NREC) = 0;
   TPP_I(I_BSTATUS) = 0;
   TPP_I(I_FSTATUS) = 0;

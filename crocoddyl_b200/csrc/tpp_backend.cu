@@ -15,8 +15,6 @@ struct TppBackend : Backend {
   std::vector<void*> allocs;
   bool solver_allocated = false;
   double* node_data[9] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  double* tmp_xs = nullptr;  // SoA scratch for the problem-level API
-  double* tmp_us = nullptr;
 
   explicit TppBackend(const ProblemDesc* p_, int sk) {
     p = p_;
@@ -54,23 +52,19 @@ struct TppBackend : Backend {
     cudaFree(q);
     q = nullptr;
   }
-  dim3 tgrid(int W, int nb) const { return dim3((nb + 31) / 32, (W + 31) / 32); }
-  void to_soa(const double* d_user, double* soa0, double* soa1, const int* cur, int flip, int W) {
-    tpp_transpose_kernel<<<tgrid(W, c.B), dim3(32, 8), 0, stream>>>(const_cast<double*>(d_user), soa0, soa1, cur,
-                                                                     flip, W, c.Bp, 0, c.B, 1);
-    ++last_launches;
-  }
-  void to_user(double* d_user, const double* soa0, const double* soa1, const int* cur, int flip, int W, int b0,
-               int nb) {
-    tpp_transpose_kernel<<<tgrid(W, nb), dim3(32, 8), 0, stream>>>(d_user, const_cast<double*>(soa0),
-                                                                    const_cast<double*>(soa1), cur, flip, W, c.Bp, b0,
-                                                                    nb, 0);
+  typedef TppLayout<M> L;
+  void gather(double* d_user, const TppFieldMap& fm, double* b0p, double* b1p, const int* sel, int flip, int b0,
+              int nb, int to_rec) {
+    tpp_gather_kernel<<<dim3((nb + 63) / 64, fm.nt), 64, 0, stream>>>(d_user, b0p, b1p, sel, flip, fm, c.Bp, b0, nb,
+                                                                       to_rec);
     ++last_launches;
   }
   int nblocks() const { return (c.B + 63) / 64; }
+  const int* cur_sel() const { return c.iscal + (size_t)I_CUR * c.Bp; }
+  const int* fs_sel() const { return c.iscal + (size_t)I_FSBUF * c.Bp; }
 
   void x0_changed() override {
-    to_soa(p->d_x0, c.x0, c.x0, nullptr, 0, N);
+    tpp_x0_kernel<<<nblocks(), 64, 0, stream>>>(p->d_x0, c.x0, N, c.B, c.Bp);
     CGX_CUDA(cudaStreamSynchronize(stream));
   }
 
@@ -78,16 +72,9 @@ struct TppBackend : Backend {
     c.o = o;
     const size_t Bp = c.Bp, T = c.T;
     if (!solver_allocated) {
-      for (int i = 0; i < 2; ++i) {
-        c.xs[i] = alloc((T + 1) * N * Bp);
-        c.us[i] = alloc(T * U * Bp);
-      }
-      c.fs = alloc((T + 1) * N * Bp);
-      c.K = alloc(T * U * N * Bp);
-      c.k = alloc(T * U * Bp);
-      c.Vx = alloc((T + 1) * N * Bp);
-      c.Vxx = alloc((T + 1) * N * N * Bp);
-      c.w = alloc((T + 1) * N * Bp);
+      for (int i = 0; i < 2; ++i) c.xu[i] = alloc((T + 1) * Bp * L::R_XU);
+      c.kk = alloc(T * Bp * L::R_KK);
+      c.v = alloc((T + 1) * Bp * L::R_V);
       c.scal = alloc((size_t)S_NSLOTS * Bp);
       int* is = dalloc<int>((size_t)I_NSLOTS * Bp);
       allocs.push_back(is);
@@ -104,13 +91,7 @@ struct TppBackend : Backend {
       CGX_CUDA(cudaStreamSynchronize(stream));
       solver_allocated = true;
     }
-    if (full && !c.Qxx) {
-      c.Qxx = alloc(T * N * N * Bp);
-      c.Qxu = alloc(T * N * U * Bp);
-      c.Quu = alloc(T * U * U * Bp);
-      c.Qx = alloc(T * N * Bp);
-      c.Qu = alloc(T * U * Bp);
-    }
+    if (full && !c.q) c.q = alloc(T * Bp * L::R_Q);
     c.full = full;
     if (trace_on && (!c.trace || c.trace_cap != trace_cap)) {
       release(c.trace);
@@ -127,14 +108,9 @@ struct TppBackend : Backend {
     const size_t Bp = c.Bp, T = c.T;
     tpp_reset_kernel<<<(c.Bp + 63) / 64, 64, 0, stream>>>(c, is_feasible);
     ++last_launches;
-    if (d_xs)
-      to_soa(d_xs, c.xs[0], c.xs[0], nullptr, 0, (T + 1) * N);
-    else
-      CGX_CUDA(cudaMemsetAsync(c.xs[0], 0, (T + 1) * N * Bp * sizeof(double), stream));
-    if (d_us)
-      to_soa(d_us, c.us[0], c.us[0], nullptr, 0, T * U);
-    else
-      CGX_CUDA(cudaMemsetAsync(c.us[0], 0, T * U * Bp * sizeof(double), stream));
+    if (!d_xs || !d_us) CGX_CUDA(cudaMemsetAsync(c.xu[0], 0, (T + 1) * Bp * L::R_XU * sizeof(double), stream));
+    if (d_xs) gather(const_cast<double*>(d_xs), fmap("xs"), c.xu[0], c.xu[0], nullptr, 0, 0, c.B, 1);
+    if (d_us) gather(const_cast<double*>(d_us), fmap("us"), c.xu[0], c.xu[0], nullptr, 0, 0, c.B, 1);
   }
 
   void solve(int maxiter, int is_feasible, double reginit) override {
@@ -163,46 +139,76 @@ struct TppBackend : Backend {
   }
 
   struct Fld {
+    TppFieldMap fm;
     double* a;
-    double* b;  // second buffer for double-buffered fields
-    int flip;   // 0: candidate, 1: trial
-    int size, nt;
-    bool dbl;
+    double* b;
+    const int* sel;
+    int flip;
   };
+  TppFieldMap fmap(const std::string& n) { return fld(n).fm; }
   Fld fld(const std::string& n) {
     const int T = c.T;
-    if (n == "xs") return {c.xs[0], c.xs[1], 0, N, T + 1, true};
-    if (n == "xs_try") return {c.xs[0], c.xs[1], 1, N, T + 1, true};
-    if (n == "us") return {c.us[0], c.us[1], 0, U, T, true};
-    if (n == "us_try") return {c.us[0], c.us[1], 1, U, T, true};
-    if (n == "fs") return {c.fs, c.fs, 0, N, T + 1, false};
-    if (n == "K") return {c.K, c.K, 0, U * N, T, false};
-    if (n == "k") return {c.k, c.k, 0, U, T, false};
-    if (n == "Vx") return {c.Vx, c.Vx, 0, N, T + 1, false};
-    if (n == "Vxx") return {c.Vxx, c.Vxx, 0, N * N, T + 1, false};
+    Fld f;
+    f.sel = nullptr;
+    f.flip = 0;
+    auto seq = [&](int R, int size, int nt, int off0) {
+      f.fm.R = R;
+      f.fm.size = size;
+      f.fm.nt = nt;
+      if (size > 16) throw Unsupported("field too wide for the thread-per-problem backend");
+      for (int i = 0; i < size; ++i) f.fm.off[i] = off0 + i;
+    };
+    if (n == "xs" || n == "xs_try" || n == "us" || n == "us_try" || n == "fs") {
+      f.a = c.xu[0];
+      f.b = c.xu[1];
+      f.sel = (n == "fs") ? fs_sel() : cur_sel();
+      f.flip = (n == "xs_try" || n == "us_try") ? 1 : 0;
+      if (n[0] == 'x') seq(L::R_XU, N, T + 1, L::XU_X);
+      else if (n[0] == 'u') seq(L::R_XU, U, T, L::XU_U);
+      else seq(L::R_XU, N, T + 1, L::XU_F);
+      return f;
+    }
+    if (n == "K" || n == "k") {
+      f.a = f.b = c.kk;
+      if (n == "K") seq(L::R_KK, U * N, T, L::KK_K);
+      else seq(L::R_KK, U, T, L::KK_k);
+      return f;
+    }
+    if (n == "Vx" || n == "Vxx") {
+      f.a = f.b = c.v;
+      if (n == "Vx") {
+        seq(L::R_V, N, T + 1, L::V_VX);
+      } else {
+        seq(L::R_V, N * N, T + 1, 0);
+        for (int j = 0; j < N; ++j)
+          for (int i = 0; i < N; ++i) f.fm.off[i + N * j] = L::V_VXX + L::sym(i, j);
+      }
+      return f;
+    }
     if (n == "Qxx" || n == "Qxu" || n == "Quu" || n == "Qx" || n == "Qu") {
-      if (!c.full || !c.Qxx)
-        throw Unsupported("field " + n + " is not kept with cgx_solver_set_storage(full = 0)");
-      if (n == "Qxx") return {c.Qxx, c.Qxx, 0, N * N, T, false};
-      if (n == "Qxu") return {c.Qxu, c.Qxu, 0, N * U, T, false};
-      if (n == "Quu") return {c.Quu, c.Quu, 0, U * U, T, false};
-      if (n == "Qx") return {c.Qx, c.Qx, 0, N, T, false};
-      return {c.Qu, c.Qu, 0, U, T, false};
+      if (!c.full || !c.q) throw Unsupported("field " + n + " is not kept with cgx_solver_set_storage(full = 0)");
+      f.a = f.b = c.q;
+      if (n == "Qxx") seq(L::R_Q, N * N, T, L::Q_XX);
+      else if (n == "Qxu") seq(L::R_Q, N * U, T, L::Q_XU);
+      else if (n == "Quu") seq(L::R_Q, U * U, T, L::Q_UU);
+      else if (n == "Qx") seq(L::R_Q, N, T, L::Q_X);
+      else seq(L::R_Q, U, T, L::Q_U);
+      return f;
     }
     throw NotFound("unknown field " + n);
   }
   FieldInfo field_info(const std::string& name) override {
     Fld f = fld(name);
-    return {f.size, f.nt};
+    return {f.fm.size, f.fm.nt};
   }
   void export_field(const std::string& name, int b0, int nb, double* d_out) override {
     Fld f = fld(name);
-    to_user(d_out, f.a, f.b, f.dbl ? c.iscal + (size_t)I_CUR * c.Bp : nullptr, f.flip, f.size * f.nt, b0, nb);
+    gather(d_out, f.fm, f.a, f.b, f.sel, f.flip, b0, nb, 0);
   }
   void import_field(const std::string& name, const double* d_in) override {
     if (name != "xs" && name != "us") throw Unsupported("only xs and us can be set");
     Fld f = fld(name);
-    to_soa(d_in, f.a, f.b, c.iscal + (size_t)I_CUR * c.Bp, 0, f.size * f.nt);
+    gather(const_cast<double*>(d_in), f.fm, f.a, f.b, f.sel, f.flip, 0, c.B, 1);
   }
   void export_scalars(double* d_out) override;
   void export_status(int which, int* d_out) override {
@@ -213,19 +219,10 @@ struct TppBackend : Backend {
   void export_trace(int b, double* d_out) override;
 
   // ---- problem-level API ----
-  void ensure_tmp() {
-    if (!tmp_xs) {
-      tmp_xs = alloc((size_t)(c.T + 1) * N * c.Bp);
-      tmp_us = alloc((size_t)c.T * U * c.Bp);
-    }
-  }
   void problem_calc(const double* d_xs, const double* d_us, int diff, double* d_costs) override;
   void problem_rollout(const double* d_us, double* d_xs) override {
-    ensure_tmp();
-    to_soa(d_us, tmp_us, tmp_us, nullptr, 0, c.T * U);
-    tpp_rollout_kernel<M><<<nblocks(), 64, 0, stream>>>(c, tmp_us, tmp_xs);
+    tpp_rollout_kernel<M><<<nblocks(), 64, 0, stream>>>(c, d_us, d_xs);
     ++last_launches;
-    to_user(d_xs, tmp_xs, tmp_xs, nullptr, 0, (c.T + 1) * N, 0, c.B);
   }
   void problem_quasi_static(const double*, double*) override {
     throw Unsupported("quasiStatic is not implemented for this model family");
@@ -314,15 +311,12 @@ void TppBackend<M>::export_trace(int b, double* d_out) {
 }
 template <class M>
 void TppBackend<M>::problem_calc(const double* d_xs, const double* d_us, int diff, double* d_costs) {
-  ensure_tmp();
   const size_t nodes = (size_t)c.B * (c.T + 1);
   const int sizes[9] = {1, N, N * N, N * U, N, U, N * N, N * U, U * U};
   for (int i = 0; i < 9; ++i)
     if (!node_data[i]) node_data[i] = alloc(nodes * sizes[i]);
-  to_soa(d_xs, tmp_xs, tmp_xs, nullptr, 0, (c.T + 1) * N);
-  to_soa(d_us, tmp_us, tmp_us, nullptr, 0, c.T * U);
   tpp_node_data_kernel<M><<<dim3(nblocks(), c.T + 1), 64, 0, stream>>>(
-      c, tmp_xs, tmp_us, diff, node_data[0], node_data[1], node_data[2], node_data[3], node_data[4], node_data[5],
+      c, d_xs, d_us, diff, node_data[0], node_data[1], node_data[2], node_data[3], node_data[4], node_data[5],
       node_data[6], node_data[7], node_data[8]);
   ++last_launches;
   tpp_cost_sum_kernel<<<nblocks(), 64, 0, stream>>>(c.B, c.T, node_data[0], d_costs);

@@ -1,0 +1,941 @@
+// crocoddyl_b200 — CTA-per-problem DDP/FDDP core for dense node models (LQR n <= ~72, revolute-chain arm).
+//
+// One thread block owns one OCP and runs the reference's whole solve() loop on the device; the block's
+// threads cooperate on the dense algebra of each node (Vxx, Fx^T Vxx, Fx staged in shared memory, register-
+// tiled DFMA products) and on the node-parallel parts (calc / calcDiff of all T+1 nodes at once).
+// HBM layout = the host layout of the C ABI: per problem contiguous, [B][nt][size], matrices column-major,
+// so a block streams its own problem with coalesced accesses and accessors are plain copies.
+//
+// Reference functions restated here (paths relative to the reference tree):
+//   ShootingProblem::calc/calcDiff              include/crocoddyl/core/optctrl/shooting.hxx:133-195
+//   SolverDDP::calcDiff/backwardPass/computeGains  src/core/solvers/ddp.cpp:157-253,298-310
+//   SolverDDP::forwardPass / SolverFDDP::forwardPass  ddp.cpp:255-296, fddp.cpp:149-225
+//   expectedImprovement / updateExpectedImprovement / stoppingCriteria  ddp.cpp:132-155, fddp.cpp:107-147
+//   SolverDDP::solve / SolverFDDP::solve        ddp.cpp:41-118, fddp.cpp:19-105
+#pragma once
+#include <stdexcept>
+#include <string>
+#include "common.cuh"
+
+namespace cgx {
+
+struct CtaCtx {
+  int B, Bp, T, n, m;
+  int fddp, full;
+  int model_kind;         // 0 LQR, 2 ARM
+  double* xs[2];          // [B][T+1][n] candidate / trial (I_CUR)
+  double* us[2];          // [B][T][m]
+  double* fs;             // [B][T+1][n]
+  double* K;              // [B][T][m*n]
+  double* k;              // [B][T][m]
+  double* Vx;             // [B][T+1][n]
+  double* Vxx;            // [B][T+1][n*n]
+  double* w;              // [B][T+1][n]  Vxx fs
+  double* Qxx;            // full only: [B][T][n*n]
+  double* Qxu;            // [B][T][n*m]
+  double* Quu;            // [B][T][m*m]
+  double* Qx;             // [B][T][n]
+  double* Qu;             // [B][T][m]
+  // ActionData of every node (core/action-base.hpp:101-142)
+  double* d_cost;         // [B][T+1]
+  double* d_xnext;        // [B][T+1][n]
+  double* d_Lx;           // [B][T+1][n]
+  double* d_Lu;           // [B][T+1][m]
+  double* d_Fx;           // per-node matrices, only for models whose derivatives vary along the horizon
+  double* d_Fu;
+  double* d_Lxx;
+  double* d_Lxu;
+  double* d_Luu;
+  const double* params;   // model parameter block(s)
+  long nparams;
+  int per_problem;
+  const double* x0;       // [B][n]
+  double* scal;           // [S_NSLOTS][Bp]
+  int* iscal;             // [I_NSLOTS][Bp]
+  double* trace;          // [B][cap][NTRACE] or null
+  int trace_cap;
+  SolverOpts o;
+};
+
+// pointers to the derivative matrices of one node (column-major, leading dimension = rows)
+struct NodeMats {
+  const double* Fx;
+  const double* Fu;
+  const double* Lxx;
+  const double* Lxu;
+  const double* Luu;
+  bool constant;  // the same for every running node of the problem (LQR): stage once
+};
+
+__device__ __forceinline__ int cta_ld(int rows) { return rows | 1; }  // odd leading dimension: no bank conflicts
+
+// ---------------------------------------------------------------------------------------------
+// Register-tiled product in shared memory, all threads of the block:
+//   C(i,j) = Add(i,j) + alpha * sum_k opA(i,k) * B(k,j)      i < M, j < N, k ascending (the oracle's order)
+// opA = A^T if TA (A is K x M) else A (M x K). A, B, C in shared memory with leading dims lda, ldb, ldc;
+// Add (may be null, may be global memory or C itself) with leading dim ldadd.
+template <bool TA>
+__device__ void cta_gemm(double* C, int ldc, const double* A, int lda, const double* B, int ldb, int M, int N, int K,
+                         const double* Add, int ldadd, double alpha) {
+  const int tm = (M + 3) >> 2, tn = (N + 3) >> 2;
+  for (int tile = threadIdx.x; tile < tm * tn; tile += blockDim.x) {
+    const int i0 = (tile % tm) << 2, j0 = (tile / tm) << 2;
+    double acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) acc[a][b] = 0.;
+    // clamp the operand indices of partial tiles (results of the clamped lanes are discarded)
+    int ia[4], jb[4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      ia[a] = min(i0 + a, M - 1);
+      jb[a] = min(j0 + a, N - 1);
+    }
+    for (int kk = 0; kk < K; ++kk) {
+      double av[4], bv[4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        av[a] = TA ? A[kk + lda * ia[a]] : A[ia[a] + lda * kk];
+        bv[a] = B[kk + ldb * jb[a]];
+      }
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] += av[a] * bv[b];
+    }
+#pragma unroll
+    for (int b = 0; b < 4; ++b)
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        const int i = i0 + a, j = j0 + b;
+        if (i < M && j < N) {
+          const double base = Add ? Add[i + ldadd * j] : 0.;
+          C[i + ldc * j] = base + alpha * acc[a][b];
+        }
+      }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// ActionModelLQR (reference: include/crocoddyl/core/actions/lqr.hxx:14-70, lqr.hpp:88-95).
+// params = [drift_free, Fx(n*n), Fu(n*m), f0(n), Lxx(n*n), Lxu(n*m), Luu(m*m), lx(n), lu(m)], column-major.
+struct LqrModel {
+  static constexpr bool kPerNodeMats = false;
+  const double *Fx, *Fu, *f0, *Lxx, *Lxu, *Luu, *lx, *lu;
+  bool drift_free;
+  int n, m;
+  // host side: device address of a constant derivative matrix (ActionDataLQR holds copies, lqr.hxx:65-69)
+  template <class PD>
+  static const double* node_matrix(const CtaCtx& c, const PD*, const std::string& name, int b, int) {
+    const size_t n = c.n, m = c.m;
+    const double* p = c.params + (c.per_problem ? (size_t)b * c.nparams : 0);
+    if (name == "Fx") return p + 1;
+    if (name == "Fu") return p + 1 + n * n;
+    if (name == "Lxx") return p + 1 + n * n + n * m + n;
+    if (name == "Lxu") return p + 1 + 2 * n * n + n * m + n;
+    return p + 1 + 2 * n * n + 2 * n * m + n;  // Luu
+  }
+  template <class BE>
+  static void quasi_static(BE&, const CtaCtx&, const double*, double*, cudaStream_t) {
+    throw std::runtime_error("quasiStatic is not implemented for ActionModelLQR");
+  }
+  __device__ void load(const CtaCtx& c, int b) {
+    n = c.n;
+    m = c.m;
+    const double* p = c.params + (c.per_problem ? (size_t)b * c.nparams : 0);
+    drift_free = p[0] != 0.;
+    Fx = p + 1;
+    Fu = Fx + n * n;
+    f0 = Fu + n * m;
+    Lxx = f0 + n;
+    Lxu = Lxx + n * n;
+    Luu = Lxu + n * m;
+    lx = Luu + m * m;
+    lu = lx + n;
+  }
+  __device__ NodeMats mats(const CtaCtx&, int, int) const { return NodeMats{Fx, Fu, Lxx, Lxu, Luu, true}; }
+
+  // calc of one node by ONE thread, in the oracle's operation order (lqr.hxx:31-49). u == nullptr: zeros.
+  __device__ double calc_serial(const double* x, const double* u, double* xnext) const {
+    for (int i = 0; i < n; ++i) {
+      double a = 0., bsum = 0.;
+      for (int j = 0; j < n; ++j) a += Fx[i + n * j] * x[j];
+      if (u)
+        for (int j = 0; j < m; ++j) bsum += Fu[i + n * j] * u[j];
+      xnext[i] = drift_free ? (a + bsum) : (a + bsum + f0[i]);
+    }
+    double xLx = 0., uLu = 0., xLu = 0., lxx_ = 0., luu_ = 0.;
+    for (int i = 0; i < n; ++i) {
+      double s = 0., s2 = 0.;
+      for (int j = 0; j < n; ++j) s += Lxx[i + n * j] * x[j];
+      if (u)
+        for (int j = 0; j < m; ++j) s2 += Lxu[i + n * j] * u[j];
+      xLx += x[i] * s;
+      xLu += x[i] * s2;
+      lxx_ += lx[i] * x[i];
+    }
+    if (u)
+      for (int i = 0; i < m; ++i) {
+        double s = 0.;
+        for (int j = 0; j < m; ++j) s += Luu[i + m * j] * u[j];
+        uLu += u[i] * s;
+        luu_ += lu[i] * u[i];
+      }
+    return 0.5 * xLx + 0.5 * uLu + xLu + lxx_ + luu_;
+  }
+  // Lx, Lu of one node by one thread (lqr.hxx:63-64); the five matrices are the model's constants
+  __device__ void calcdiff_serial(const double* x, const double* u, double* Lx, double* Lu) const {
+    for (int i = 0; i < n; ++i) {
+      double a = 0., bsum = 0.;
+      for (int j = 0; j < n; ++j) a += Lxx[i + n * j] * x[j];
+      if (u)
+        for (int j = 0; j < m; ++j) bsum += Lxu[i + n * j] * u[j];
+      Lx[i] = lx[i] + a + bsum;
+    }
+    for (int i = 0; i < m; ++i) {
+      double cc = 0., e = 0.;
+      for (int j = 0; j < n; ++j) cc += Lxu[j + n * i] * x[j];
+      if (u)
+        for (int j = 0; j < m; ++j) e += Luu[i + m * j] * u[j];
+      Lu[i] = lu[i] + cc + e;
+    }
+  }
+  // all nodes of the problem at once: one node per thread (ShootingProblem::calc, shooting.hxx:133-161)
+  __device__ void calc_all(const CtaCtx& c, int b, const double* xs, const double* us) const {
+    const int T = c.T;
+    for (int t = threadIdx.x; t <= T; t += blockDim.x) {
+      const size_t node = (size_t)b * (T + 1) + t;
+      c.d_cost[node] = calc_serial(xs + (size_t)t * n, t < T ? us + (size_t)t * m : nullptr, c.d_xnext + node * n);
+    }
+  }
+  __device__ void calcdiff_all(const CtaCtx& c, int b, const double* xs, const double* us) const {
+    const int T = c.T;
+    for (int t = threadIdx.x; t <= T; t += blockDim.x) {
+      const size_t node = (size_t)b * (T + 1) + t;
+      calcdiff_serial(xs + (size_t)t * n, t < T ? us + (size_t)t * m : nullptr, c.d_Lx + node * n, c.d_Lu + node * m);
+    }
+  }
+  // calc of one node by the whole block (rollout): x, u in shared memory; writes xnext (shared), returns the
+  // cost to thread 0 through *cost_out (shared). scratch: >= 2n+m doubles of shared memory.
+  __device__ void calc_block(const double* x, const double* u, double* xnext, double* scratch, double* cost_out) const {
+    double* Lxx_x = scratch;
+    double* Lxu_u = scratch + n;
+    double* Luu_u = scratch + 2 * n;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      double a = 0., bsum = 0., s = 0., s2 = 0.;
+      for (int j = 0; j < n; ++j) {
+        a += Fx[i + n * j] * x[j];
+        s += Lxx[i + n * j] * x[j];
+      }
+      if (u)
+        for (int j = 0; j < m; ++j) {
+          bsum += Fu[i + n * j] * u[j];
+          s2 += Lxu[i + n * j] * u[j];
+        }
+      xnext[i] = drift_free ? (a + bsum) : (a + bsum + f0[i]);
+      Lxx_x[i] = s;
+      Lxu_u[i] = s2;
+    }
+    if (u)
+      for (int i = threadIdx.x; i < m; i += blockDim.x) {
+        double s = 0.;
+        for (int j = 0; j < m; ++j) s += Luu[i + m * j] * u[j];
+        Luu_u[i] = s;
+      }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double xLx = 0., uLu = 0., xLu = 0., lxx_ = 0., luu_ = 0.;
+      for (int i = 0; i < n; ++i) {
+        xLx += x[i] * Lxx_x[i];
+        xLu += x[i] * Lxu_u[i];
+        lxx_ += lx[i] * x[i];
+      }
+      if (u)
+        for (int i = 0; i < m; ++i) {
+          uLu += u[i] * Luu_u[i];
+          luu_ += lu[i] * u[i];
+        }
+      *cost_out = 0.5 * xLx + 0.5 * uLu + xLu + lxx_ + luu_;
+    }
+    __syncthreads();
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// Shared-memory work area of one block (doubles). Leading dimensions are odd (cta_ld).
+struct CtaSmem {
+  double *V, *A, *Fx, *Fu, *Qxu, *G, *Kg, *Quu, *Lc;  // matrices
+  double *Vx, *Qx, *Qu, *kg, *Quuk, *x, *u, *dx, *xn, *scr;  // vectors
+  double* red;   // 8 doubles of reduction / broadcast scratch
+  int* flag;
+  int ldn, ldm;
+  __device__ static size_t doubles(int n, int m) {
+    const size_t ldn = n | 1, ldm = (m | 1);
+    return 3 * ldn * n + 2 * ldn * m + 2 * ldm * n + 2 * ldm * m + 6 * (size_t)n + 4 * (size_t)m + (2 * n + m) + 16;
+  }
+  __device__ void carve(double* base, int n, int m) {
+    ldn = n | 1;
+    ldm = m | 1;
+    double* p = base;
+    V = p; p += ldn * n;
+    A = p; p += ldn * n;
+    Fx = p; p += ldn * n;
+    Fu = p; p += ldn * m;
+    Qxu = p; p += ldn * m;
+    G = p; p += ldm * n;
+    Kg = p; p += ldm * n;
+    Quu = p; p += ldm * m;
+    Lc = p; p += ldm * m;
+    Vx = p; p += n;
+    Qx = p; p += n;
+    x = p; p += n;
+    dx = p; p += n;
+    xn = p; p += n;
+    p += n;  // spare
+    Qu = p; p += m;
+    kg = p; p += m;
+    Quuk = p; p += m;
+    u = p; p += m;
+    scr = p; p += 2 * n + m;
+    red = p; p += 8;
+    flag = reinterpret_cast<int*>(p);
+  }
+};
+inline size_t cta_smem_bytes(int n, int m) {
+  const size_t ldn = n | 1, ldm = (m | 1);
+  return 8 * (3 * ldn * n + 2 * ldn * m + 2 * ldm * n + 2 * ldm * m + 6 * (size_t)n + 4 * (size_t)m + (2 * n + m) + 16);
+}
+
+// copy a column-major rows x cols matrix from global memory to shared memory (leading dim ld)
+__device__ __forceinline__ void cta_stage(double* dst, int ld, const double* src, int rows, int cols) {
+  for (int e = threadIdx.x; e < rows * cols; e += blockDim.x) dst[(e % rows) + ld * (e / rows)] = src[e];
+}
+__device__ __forceinline__ void cta_unstage(double* dst, const double* src, int ld, int rows, int cols) {
+  for (int e = threadIdx.x; e < rows * cols; e += blockDim.x) dst[e] = src[(e % rows) + ld * (e / rows)];
+}
+
+// ---------------------------------------------------------------------------------------------
+// SolverDDP::calcDiff (ddp.cpp:157-178) for one problem: calc (only when do_calc: iter_ == 0), calcDiff of all
+// nodes, total cost in the reference's order (shooting.hxx:188-192) and the gaps fs. Returns the cost to all.
+template <class M>
+__device__ double cta_calcdiff(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, int cur, bool do_calc,
+                               bool is_feasible, bool was_feasible) {
+  const int T = c.T, n = c.n, m = c.m;
+  const double* xs = c.xs[cur] + (size_t)b * (T + 1) * n;
+  const double* us = c.us[cur] + (size_t)b * T * m;
+  if (do_calc) mod.calc_all(c, b, xs, us);
+  mod.calcdiff_all(c, b, xs, us);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double cost = 0.;
+    for (int t = 0; t <= T; ++t) cost += c.d_cost[(size_t)b * (T + 1) + t];
+    sm.red[0] = cost;
+  }
+  double* fs = c.fs + (size_t)b * (T + 1) * n;
+  if (!is_feasible) {
+    const double* xnext = c.d_xnext + (size_t)b * (T + 1) * n;
+    for (int e = threadIdx.x; e < (T + 1) * n; e += blockDim.x) {
+      const int t = e / n, i = e % n;
+      fs[e] = (t == 0) ? (c.x0[(size_t)b * n + i] - xs[i]) : (xnext[(size_t)(t - 1) * n + i] - xs[e]);
+    }
+  } else if (!was_feasible) {
+    for (int e = threadIdx.x; e < (T + 1) * n; e += blockDim.x) fs[e] = 0.;
+  }
+  __syncthreads();
+  return sm.red[0];
+}
+
+// ---------------------------------------------------------------------------------------------
+// SolverDDP::backwardPass + computeGains (ddp.cpp:180-253,298-310) for one problem by the whole block, with the
+// reductions of updateExpectedImprovement (fddp.cpp:126-147) / expectedImprovement (ddp.cpp:144-155) /
+// stoppingCriteria (ddp.cpp:132-142). Returns 0 or 1 ("backward_error") to all threads; dg,dq,stop valid on
+// every thread.
+template <class M>
+__device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, bool is_feasible, double xreg,
+                            double ureg, double& dg_out, double& dq_out, double& stop_out) {
+  const int T = c.T, n = c.n, m = c.m, ldn = sm.ldn, ldm = sm.ldm;
+  const int tid = threadIdx.x, P = blockDim.x;
+  const bool fddp = c.fddp != 0, full = c.full != 0;
+  const bool has_xreg = !isnan(xreg), has_ureg = !isnan(ureg);
+  const double* fs = c.fs + (size_t)b * (T + 1) * n;
+  double dg = 0., dq = 0., stop = 0.;  // thread 0 accumulates
+  // ---- terminal node (ddp.cpp:181-191)
+  {
+    const NodeMats nm = mod.mats(c, b, T);
+    cta_stage(sm.V, ldn, nm.Lxx, n, n);
+    for (int i = tid; i < n; i += P) sm.Vx[i] = c.d_Lx[((size_t)b * (T + 1) + T) * n + i];
+    __syncthreads();
+    if (has_xreg)
+      for (int i = tid; i < n; i += P) sm.V[i + ldn * i] += xreg;
+    __syncthreads();
+    if (!is_feasible) {
+      for (int i = tid; i < n; i += P) {
+        double s = 0.;
+        for (int j = 0; j < n; ++j) s += sm.V[i + ldn * j] * fs[(size_t)T * n + j];
+        sm.scr[i] = s;
+        sm.Vx[i] += s;
+      }
+      __syncthreads();
+    }
+    for (int i = tid; i < n; i += P) {
+      c.Vx[((size_t)b * (T + 1) + T) * n + i] = sm.Vx[i];
+      c.w[((size_t)b * (T + 1) + T) * n + i] = is_feasible ? 0. : sm.scr[i];
+    }
+    cta_unstage(c.Vxx + ((size_t)b * (T + 1) + T) * n * n, sm.V, ldn, n, n);
+    if (tid == 0 && fddp && !is_feasible) {  // fddp.cpp:131-135
+      double a = 0., q = 0.;
+      for (int i = 0; i < n; ++i) {
+        a += sm.Vx[i] * fs[(size_t)T * n + i];
+        q += fs[(size_t)T * n + i] * sm.scr[i];
+      }
+      dg -= a;
+      dq += q;
+    }
+    __syncthreads();
+  }
+  bool staged = false;
+  for (int t = T - 1; t >= 0; --t) {
+    const NodeMats nm = mod.mats(c, b, t);
+    const size_t node = (size_t)b * (T + 1) + t, rnode = (size_t)b * T + t;
+    if (!(nm.constant && staged)) {
+      cta_stage(sm.Fx, ldn, nm.Fx, n, n);
+      cta_stage(sm.Fu, ldn, nm.Fu, n, m);
+      staged = true;
+    }
+    __syncthreads();
+    // A = Fx^T Vxx' ; G = Fu^T Vxx' ; Qx = Lx + Fx^T Vx' ; Qu = Lu + Fu^T Vx'   (ddp.cpp:204,206,211,214)
+    cta_gemm<true>(sm.A, ldn, sm.Fx, ldn, sm.V, ldn, n, n, n, nullptr, 0, 1.);
+    cta_gemm<true>(sm.G, ldm, sm.Fu, ldn, sm.V, ldn, m, n, n, nullptr, 0, 1.);
+    for (int j = tid; j < n + m; j += P) {
+      double s = 0.;
+      if (j < n) {
+        for (int i = 0; i < n; ++i) s += sm.Fx[i + ldn * j] * sm.Vx[i];
+        sm.Qx[j] = c.d_Lx[node * n + j] + s;
+      } else {
+        const int jj = j - n;
+        for (int i = 0; i < n; ++i) s += sm.Fu[i + ldn * jj] * sm.Vx[i];
+        sm.Qu[jj] = c.d_Lu[node * m + jj] + s;
+      }
+    }
+    __syncthreads();
+    // Qxx = Lxx + A Fx (into V: Vxx' is dead) ; Qxu = Lxu + A Fu ; Quu = Luu + G Fu (+ ureg)   (ddp.cpp:202-218)
+    cta_gemm<false>(sm.V, ldn, sm.A, ldn, sm.Fx, ldn, n, n, n, nm.Lxx, n, 1.);
+    cta_gemm<false>(sm.Qxu, ldn, sm.A, ldn, sm.Fu, ldn, n, m, n, nm.Lxu, n, 1.);
+    cta_gemm<false>(sm.Quu, ldm, sm.G, ldm, sm.Fu, ldn, m, m, n, nm.Luu, m, 1.);
+    __syncthreads();
+    if (has_ureg)
+      for (int i = tid; i < m; i += P) sm.Quu[i + ldm * i] += ureg;
+    if (tid == 0) *sm.flag = 0;
+    __syncthreads();
+    if (full) {
+      cta_unstage(c.Qxx + rnode * n * n, sm.V, ldn, n, n);
+      cta_unstage(c.Qxu + rnode * n * m, sm.Qxu, ldn, n, m);
+      cta_unstage(c.Quu + rnode * m * m, sm.Quu, ldm, m, m);
+      for (int i = tid; i < n; i += P) c.Qx[rnode * n + i] = sm.Qx[i];
+      for (int i = tid; i < m; i += P) c.Qu[rnode * m + i] = sm.Qu[i];
+    }
+    // computeGains (ddp.cpp:298-310): unblocked lower LLT by warp 0, lane i owns row i (rows i, i+32, ...)
+    if (tid < 32) {
+      for (int e = tid; e < m * m; e += 32) sm.Lc[(e % m) + ldm * (e / m)] = sm.Quu[(e % m) + ldm * (e / m)];
+      __syncwarp();
+      for (int kk = 0; kk < m; ++kk) {
+        double p = sm.Lc[kk + ldm * kk];
+        for (int j = 0; j < kk; ++j) p -= sm.Lc[kk + ldm * j] * sm.Lc[kk + ldm * j];
+        if (p <= 0.) *sm.flag = 1;
+        p = sqrt(p);
+        __syncwarp();
+        if (tid == 0) sm.Lc[kk + ldm * kk] = p;
+        for (int i = kk + 1 + tid; i < m; i += 32) {
+          double s = sm.Lc[i + ldm * kk];
+          for (int j = 0; j < kk; ++j) s -= sm.Lc[i + ldm * j] * sm.Lc[kk + ldm * j];
+          sm.Lc[i + ldm * kk] = s / p;
+        }
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+    if (*sm.flag) return 1;
+    // K = Quu^-1 Qxu^T, k = Quu^-1 Qu: one right-hand side per thread (in-place forward/back substitution)
+    for (int col = tid; col <= n; col += P) {
+      double* r = (col < n) ? (sm.Kg + ldm * col) : sm.kg;
+      for (int i = 0; i < m; ++i) r[i] = (col < n) ? sm.Qxu[col + ldn * i] : sm.Qu[i];
+      for (int i = 0; i < m; ++i) {
+        double s = r[i];
+        for (int j = 0; j < i; ++j) s -= sm.Lc[i + ldm * j] * r[j];
+        r[i] = s / sm.Lc[i + ldm * i];
+      }
+      for (int i = m - 1; i >= 0; --i) {
+        double s = r[i];
+        for (int j = i + 1; j < m; ++j) s -= sm.Lc[j + ldm * i] * r[j];
+        r[i] = s / sm.Lc[i + ldm * i];
+      }
+    }
+    __syncthreads();
+    for (int i = tid; i < m; i += P) {
+      double s = 0.;
+      for (int j = 0; j < m; ++j) s += sm.Quu[i + ldm * j] * sm.kg[j];
+      sm.Quuk[i] = s;  // ddp.cpp:229
+    }
+    __syncthreads();
+    // Vx = Qx + K^T Quuk - 2 K^T Qu ; Vxx = Qxx - Qxu K   (ddp.cpp:223-233)
+    for (int j = tid; j < n; j += P) {
+      double s1 = 0., s2 = 0.;
+      for (int i = 0; i < m; ++i) {
+        s1 += sm.Kg[i + ldm * j] * sm.Quuk[i];
+        s2 += sm.Kg[i + ldm * j] * sm.Qu[i];
+      }
+      double v = sm.Qx[j];
+      if (has_ureg) {
+        v += s1;
+        v += -2. * s2;
+      } else {
+        v += -1. * s2;
+      }
+      sm.Vx[j] = v;
+    }
+    cta_gemm<false>(sm.V, ldn, sm.Qxu, ldn, sm.Kg, ldm, n, n, m, sm.V, ldn, -1.);
+    if (tid == 0) {  // ddp.cpp:132-155 / fddp.cpp:137-140
+      double a = 0., q = 0., st = 0.;
+      for (int i = 0; i < m; ++i) {
+        a += sm.Qu[i] * sm.kg[i];
+        q += sm.kg[i] * sm.Quuk[i];
+        st += sm.Qu[i] * sm.Qu[i];
+      }
+      dg += a;
+      dq -= q;
+      stop += st;
+    }
+    __syncthreads();
+    // Vxx = .5 (Vxx + Vxx^T) ; diag += xreg   (ddp.cpp:235-239)
+    for (int e = tid; e < n * n; e += P) {
+      const int i = e % n, j = e / n;
+      if (i > j) {
+        const double s = 0.5 * (sm.V[i + ldn * j] + sm.V[j + ldn * i]);
+        sm.V[i + ldn * j] = s;
+        sm.V[j + ldn * i] = s;
+      } else if (i == j) {
+        double s = 0.5 * (sm.V[i + ldn * i] + sm.V[i + ldn * i]);
+        if (has_xreg) s += xreg;
+        sm.V[i + ldn * i] = s;
+      }
+    }
+    __syncthreads();
+    if (!is_feasible) {  // Vx += Vxx fs[t]   (ddp.cpp:242-244)
+      for (int i = tid; i < n; i += P) {
+        double s = 0.;
+        for (int j = 0; j < n; ++j) s += sm.V[i + ldn * j] * fs[(size_t)t * n + j];
+        sm.scr[i] = s;
+        sm.Vx[i] += s;
+      }
+      __syncthreads();
+    }
+    // raiseIfNaN(|Vx|_inf), raiseIfNaN(|Vxx|_inf)   (ddp.cpp:246-251)
+    int bad = 0;
+    for (int i = tid; i < n; i += P) bad |= raise_if_nan(fabs(sm.Vx[i]));
+    for (int e = tid; e < n * n; e += P) bad |= raise_if_nan(fabs(sm.V[(e % n) + ldn * (e / n)]));
+    // stores
+    for (int i = tid; i < n; i += P) {
+      c.Vx[node * n + i] = sm.Vx[i];
+      c.w[node * n + i] = is_feasible ? 0. : sm.scr[i];
+    }
+    for (int i = tid; i < m; i += P) c.k[rnode * m + i] = sm.kg[i];
+    cta_unstage(c.Vxx + node * n * n, sm.V, ldn, n, n);
+    cta_unstage(c.K + rnode * m * n, sm.Kg, ldm, m, n);
+    if (tid == 0 && fddp && !is_feasible) {  // fddp.cpp:141-145
+      double a = 0., q = 0.;
+      for (int i = 0; i < n; ++i) {
+        a += sm.Vx[i] * fs[(size_t)t * n + i];
+        q += fs[(size_t)t * n + i] * sm.scr[i];
+      }
+      dg -= a;
+      dq += q;
+    }
+    if (__syncthreads_or(bad)) return 1;
+  }
+  if (tid == 0) {
+    sm.red[0] = dg;
+    sm.red[1] = dq;
+    sm.red[2] = stop;
+  }
+  __syncthreads();
+  dg_out = sm.red[0];
+  dq_out = sm.red[1];
+  stop_out = sm.red[2];
+  __syncthreads();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// SolverFDDP::forwardPass (fddp.cpp:149-225) / SolverDDP::forwardPass (ddp.cpp:255-296) for one problem by the
+// whole block, fused with SolverFDDP::expectedImprovement's gap term dv = sum_t w_t^T (xs_try_t - xs_t)
+// (fddp.cpp:107-124). Node data (xnext, cost) are overwritten by the trial exactly like the reference's datas.
+// Returns 0 or 1 ("forward_error") to all threads; cost_try and dv valid on every thread.
+template <class M>
+__device__ int cta_forward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, int cur, double alpha, bool is_feasible,
+                           double& cost_try_out, double& dv_out) {
+  const int T = c.T, n = c.n, m = c.m;
+  const int tid = threadIdx.x, P = blockDim.x;
+  const bool fddp = c.fddp != 0;
+  const bool closed = !fddp || is_feasible || (alpha == 1.);
+  const bool use_w = fddp && !is_feasible;
+  const double am1 = alpha - 1.;
+  const double* xs = c.xs[cur] + (size_t)b * (T + 1) * n;
+  const double* us = c.us[cur] + (size_t)b * T * m;
+  double* xt_ = c.xs[cur ^ 1] + (size_t)b * (T + 1) * n;
+  double* ut_ = c.us[cur ^ 1] + (size_t)b * T * m;
+  const double* fs = c.fs + (size_t)b * (T + 1) * n;
+  const double* w = c.w + (size_t)b * (T + 1) * n;
+  double cost_try = 0., dv = 0.;  // thread 0
+  for (int i = tid; i < n; i += P) sm.xn[i] = c.x0[(size_t)b * n + i];
+  __syncthreads();
+  for (int t = 0; t <= T; ++t) {
+    for (int i = tid; i < n; i += P) {
+      const double xt = closed ? sm.xn[i] : sm.xn[i] + fs[(size_t)t * n + i] * am1;
+      sm.x[i] = xt;
+      sm.dx[i] = xt - xs[(size_t)t * n + i];
+      xt_[(size_t)t * n + i] = xt;
+    }
+    __syncthreads();
+    if (t < T) {
+      const double* Kt = c.K + ((size_t)b * T + t) * m * n;
+      const double* kt = c.k + ((size_t)b * T + t) * m;
+      for (int i = tid; i < m; i += P) {
+        double s = 0.;
+        for (int j = 0; j < n; ++j) s += Kt[i + m * j] * sm.dx[j];
+        const double u = us[(size_t)t * m + i] - kt[i] * alpha - s;
+        sm.u[i] = u;
+        ut_[(size_t)t * m + i] = u;
+      }
+    }
+    if (tid == 0 && use_w) {
+      double s = 0.;
+      for (int i = 0; i < n; ++i) s += w[(size_t)t * n + i] * sm.dx[i];
+      dv += s;
+    }
+    __syncthreads();
+    mod.calc_block(sm.x, t < T ? sm.u : nullptr, sm.xn, sm.scr, &sm.red[3]);
+    // datas[t]->xnext / cost (overwritten by every trial)
+    const size_t node = (size_t)b * (T + 1) + t;
+    for (int i = tid; i < n; i += P) c.d_xnext[node * n + i] = sm.xn[i];
+    int bad = 0;
+    if (tid == 0) {
+      c.d_cost[node] = sm.red[3];
+      cost_try += sm.red[3];
+      bad = raise_if_nan(cost_try);
+    }
+    if (t < T)
+      for (int i = tid; i < n; i += P) bad |= raise_if_nan(fabs(sm.xn[i]));
+    if (__syncthreads_or(bad)) return 1;
+  }
+  if (tid == 0) {
+    sm.red[0] = cost_try;
+    sm.red[1] = dv;
+  }
+  __syncthreads();
+  cost_try_out = sm.red[0];
+  dv_out = sm.red[1];
+  __syncthreads();
+  return 0;
+}
+
+__device__ inline bool cta_accept(const SolverOpts& o, bool fddp, bool is_feasible, double d0, double dV, double dVexp) {
+  if (fddp) {
+    if (dVexp >= 0) return d0 < o.th_grad || dV > o.th_acceptstep * dVexp;
+    return dV > o.th_acceptnegstep * dVexp;
+  }
+  if (dVexp >= 0) return d0 < o.th_grad || !is_feasible || dV > o.th_acceptstep * dVexp;
+  return false;
+}
+
+#define CTA_S(slot) c.scal[(size_t)(slot) * c.Bp + b]
+#define CTA_I(slot) c.iscal[(size_t)(slot) * c.Bp + b]
+
+// ---------------------------------------------------------------------------------------------
+// Whole SolverDDP::solve / SolverFDDP::solve loop for one problem per block (ddp.cpp:41-118, fddp.cpp:19-105).
+// All control-flow variables are block-uniform (every thread computes the same scalars from broadcast values).
+template <class M>
+__global__ void cta_solve_kernel(const __grid_constant__ CtaCtx c, int maxiter, int is_feasible0, double reginit) {
+  extern __shared__ double cta_smem_raw[];
+  const int b = blockIdx.x;
+  CtaSmem sm;
+  sm.carve(cta_smem_raw, c.n, c.m);
+  M mod;
+  mod.load(c, b);
+  const bool fddp = c.fddp != 0;
+  int cur = CTA_I(I_CUR);
+  bool feas = is_feasible0 != 0, wasfeas = false;
+  double xreg = isnan(reginit) ? c.o.regmin : reginit, ureg = xreg;
+  double cost = CTA_S(S_COST), stop = CTA_S(S_STOP), d0 = CTA_S(S_D0), d1 = CTA_S(S_D1);
+  double steplength = CTA_S(S_STEP), dV = CTA_S(S_DV), dVexp = CTA_S(S_DVEXP), cost_try = CTA_S(S_COST_TRY);
+  double dg = 0., dq = 0.;
+  int nbwd = 0, nfwd = 0, nrec = 0, converged = 0, iter = 0;
+  bool recalc = true, done = false;
+  __syncthreads();
+  for (iter = 0; iter < maxiter && !done; ++iter) {
+    int retries = 0;
+    while (true) {  // computeDirection(recalcDiff) with regularisation retry (ddp.cpp:55-68)
+      if (recalc) cost = cta_calcdiff(c, mod, sm, b, cur, iter == 0, feas, wasfeas);
+      const int st = cta_backward(c, mod, sm, b, feas, xreg, ureg, dg, dq, stop);
+      ++nbwd;
+      if (st == 0) break;
+      recalc = false;
+      reg_increase(c.o, xreg, ureg);
+      ++retries;
+      if (xreg == c.o.regmax) {
+        done = true;
+        break;
+      }
+    }
+    if (done) break;
+    if (!fddp) {
+      d0 = dg;
+      d1 = dq;
+    }
+    recalc = false;
+    int accepted = -1;
+    for (int a = 0; a < c.o.nalphas; ++a) {
+      steplength = c.o.alphas[a];
+      double dv = 0.;
+      const int st = cta_forward(c, mod, sm, b, cur, steplength, feas, cost_try, dv);
+      ++nfwd;
+      if (st) continue;
+      dV = cost - cost_try;
+      if (fddp) {
+        d0 = dg + dv;
+        d1 = dq - 2 * dv;
+      }
+      dVexp = steplength * (d0 + 0.5 * steplength * d1);
+      if (cta_accept(c.o, fddp, feas, d0, dV, dVexp)) {
+        wasfeas = feas;
+        feas = fddp ? (wasfeas || (steplength == 1.)) : true;
+        cost = cost_try;
+        cur ^= 1;
+        recalc = true;
+        accepted = a;
+        break;
+      }
+    }
+    if (steplength > c.o.th_stepdec) reg_decrease(c.o, xreg, ureg);
+    if (steplength <= c.o.th_stepinc) {
+      reg_increase(c.o, xreg, ureg);
+      if (xreg == c.o.regmax) break;
+    }
+    if (c.trace && nrec < c.trace_cap && threadIdx.x == 0) {
+      double* tr = c.trace + ((size_t)b * c.trace_cap + nrec) * NTRACE;
+      tr[0] = iter;
+      tr[1] = cost;
+      tr[2] = stop;
+      tr[3] = d0;
+      tr[4] = d1;
+      tr[5] = xreg;
+      tr[6] = ureg;
+      tr[7] = steplength;
+      tr[8] = feas ? 1. : 0.;
+      tr[9] = dV;
+      tr[10] = dVexp;
+      tr[11] = accepted;
+      tr[12] = retries;
+    }
+    ++nrec;
+    if (wasfeas && stop < c.o.th_stop) {
+      converged = 1;
+      break;
+    }
+  }
+  if (threadIdx.x == 0) {
+    CTA_S(S_COST) = cost;
+    CTA_S(S_STOP) = stop;
+    CTA_S(S_D0) = d0;
+    CTA_S(S_D1) = d1;
+    CTA_S(S_XREG) = xreg;
+    CTA_S(S_UREG) = ureg;
+    CTA_S(S_STEP) = steplength;
+    CTA_S(S_DV) = dV;
+    CTA_S(S_DVEXP) = dVexp;
+    CTA_S(S_COST_TRY) = cost_try;
+    CTA_S(S_DG) = dg;
+    CTA_S(S_DQ) = dq;
+    CTA_I(I_ITER) = iter;
+    CTA_I(I_FEAS) = feas;
+    CTA_I(I_WASFEAS) = wasfeas;
+    CTA_I(I_CONVERGED) = converged;
+    CTA_I(I_CUR) = cur;
+    CTA_I(I_NREC) = nrec;
+    CTA_I(I_NBWD) = nbwd;
+    CTA_I(I_NFWD) = nfwd;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Step-wise kernels. what: 0 = calcDiff only, 1 = backwardPass only, 2 = computeDirection (calcDiff if recalc, then
+// backwardPass) — ddp.cpp:120-125,157-253. The step-wise API runs with iter_ == 0, so problem_->calc is evaluated.
+template <class M>
+__global__ void cta_direction_kernel(const __grid_constant__ CtaCtx c, int what, int recalc) {
+  extern __shared__ double cta_smem_raw[];
+  const int b = blockIdx.x;
+  CtaSmem sm;
+  sm.carve(cta_smem_raw, c.n, c.m);
+  M mod;
+  mod.load(c, b);
+  const int cur = CTA_I(I_CUR);
+  const bool feas = CTA_I(I_FEAS) != 0, wasfeas = CTA_I(I_WASFEAS) != 0;
+  __syncthreads();
+  if (what == 0 || (what == 2 && recalc)) {
+    const double cost = cta_calcdiff(c, mod, sm, b, cur, true, feas, wasfeas);
+    if (threadIdx.x == 0) CTA_S(S_COST) = cost;
+  }
+  if (what == 0) return;
+  double dg = 0., dq = 0., stop = 0.;
+  const int st = cta_backward(c, mod, sm, b, feas, CTA_S(S_XREG), CTA_S(S_UREG), dg, dq, stop);
+  if (threadIdx.x == 0) {
+    CTA_I(I_BSTATUS) = st;
+    ++CTA_I(I_NBWD);
+    if (st == 0) {
+      CTA_S(S_DG) = dg;
+      CTA_S(S_DQ) = dq;
+      CTA_S(S_STOP) = stop;
+      if (!c.fddp) {
+        CTA_S(S_D0) = dg;
+        CTA_S(S_D1) = dq;
+      }
+    }
+  }
+}
+
+template <class M>
+__global__ void cta_trystep_kernel(const __grid_constant__ CtaCtx c, double alpha) {
+  extern __shared__ double cta_smem_raw[];
+  const int b = blockIdx.x;
+  CtaSmem sm;
+  sm.carve(cta_smem_raw, c.n, c.m);
+  M mod;
+  mod.load(c, b);
+  const int cur = CTA_I(I_CUR);
+  const bool feas = CTA_I(I_FEAS) != 0;
+  __syncthreads();
+  double cost_try = 0., dv = 0.;
+  const int st = cta_forward(c, mod, sm, b, cur, alpha, feas, cost_try, dv);
+  if (threadIdx.x == 0) {
+    CTA_I(I_FSTATUS) = st;
+    if (st == 0) {
+      CTA_S(S_COST_TRY) = cost_try;
+      CTA_S(S_DV) = CTA_S(S_COST) - cost_try;
+      CTA_S(S_DVGAP) = dv;
+      CTA_S(S_STEP) = alpha;
+      if (c.fddp) {
+        CTA_S(S_D0) = CTA_S(S_DG) + dv;
+        CTA_S(S_D1) = CTA_S(S_DQ) - 2 * dv;
+      }
+    }
+  }
+}
+
+// ShootingProblem::calc / calcDiff on caller-provided trajectories (user layout): what 0 = calc, 1 = calcDiff
+template <class M>
+__global__ void cta_problem_kernel(const __grid_constant__ CtaCtx c, const double* xs, const double* us, int diff,
+                                   double* costs) {
+  const int b = blockIdx.x;
+  M mod;
+  mod.load(c, b);
+  const double* x = xs + (size_t)b * (c.T + 1) * c.n;
+  const double* u = us + (size_t)b * c.T * c.m;
+  if (diff)
+    mod.calcdiff_all(c, b, x, u);
+  else
+    mod.calc_all(c, b, x, u);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double cost = 0.;
+    for (int t = 0; t <= c.T; ++t) cost += c.d_cost[(size_t)b * (c.T + 1) + t];
+    costs[b] = cost;
+  }
+}
+
+// ShootingProblem::rollout (shooting.hxx:198-223) by the block
+template <class M>
+__global__ void cta_rollout_kernel(const __grid_constant__ CtaCtx c, const double* us, double* xs) {
+  extern __shared__ double cta_smem_raw[];
+  const int b = blockIdx.x, T = c.T, n = c.n, m = c.m;
+  CtaSmem sm;
+  sm.carve(cta_smem_raw, n, m);
+  M mod;
+  mod.load(c, b);
+  for (int i = threadIdx.x; i < n; i += blockDim.x) sm.x[i] = c.x0[(size_t)b * n + i];
+  __syncthreads();
+  for (int t = 0; t <= T; ++t) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) xs[((size_t)b * (T + 1) + t) * n + i] = sm.x[i];
+    if (t < T)
+      for (int i = threadIdx.x; i < m; i += blockDim.x) sm.u[i] = us[((size_t)b * T + t) * m + i];
+    __syncthreads();
+    mod.calc_block(sm.x, t < T ? sm.u : nullptr, sm.xn, sm.scr, &sm.red[3]);
+    const size_t node = (size_t)b * (T + 1) + t;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      c.d_xnext[node * n + i] = sm.xn[i];
+      if (t < T) sm.x[i] = sm.xn[i];
+    }
+    if (threadIdx.x == 0) c.d_cost[node] = sm.red[3];
+    __syncthreads();
+  }
+}
+
+// per-problem bookkeeping of setCandidate + scalar export
+__global__ void cta_reset_kernel(CtaCtx c, int is_feasible) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= c.B) return;
+  CTA_I(I_ITER) = 0;
+  CTA_I(I_FEAS) = is_feasible;
+  CTA_I(I_WASFEAS) = 0;
+  CTA_I(I_CONVERGED) = 0;
+  CTA_I(I_CUR) = 0;
+  CTA_I(I_NREC) = 0;
+  CTA_I(I_BSTATUS) = 0;
+  CTA_I(I_FSTATUS) = 0;
+  CTA_I(I_NBWD) = 0;
+  CTA_I(I_NFWD) = 0;
+  CTA_S(S_DVGAP) = 0.;
+}
+__global__ void cta_scalars_kernel(CtaCtx c, double* out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= c.B) return;
+  double* o = out + (size_t)b * 17;
+  o[0] = CTA_S(S_COST);
+  o[1] = CTA_S(S_STOP);
+  o[2] = CTA_S(S_D0);
+  o[3] = CTA_S(S_D1);
+  o[4] = CTA_S(S_XREG);
+  o[5] = CTA_S(S_UREG);
+  o[6] = CTA_S(S_STEP);
+  o[7] = CTA_S(S_DV);
+  o[8] = CTA_S(S_DVEXP);
+  o[9] = CTA_I(I_ITER);
+  o[10] = CTA_I(I_FEAS);
+  o[11] = CTA_I(I_CONVERGED);
+  o[12] = CTA_I(I_NREC);
+  o[13] = CTA_S(S_COST_TRY);
+  o[14] = CTA_I(I_WASFEAS);
+  o[15] = CTA_I(I_NBWD);
+  o[16] = CTA_I(I_NFWD);
+}
+__global__ void cta_setreg_kernel(CtaCtx c, double xreg, double ureg, int set_x, int set_u) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= c.B) return;
+  if (set_x) CTA_S(S_XREG) = xreg;
+  if (set_u) CTA_S(S_UREG) = ureg;
+}
+// out[b][...] = field of problems b0.. : per-problem contiguous copy, selecting the candidate/trial buffer
+__global__ void cta_copy_sel_kernel(double* out, const double* a0, const double* a1, const int* sel, int flip,
+                                    size_t per_problem, int b0, int to_field) {
+  const int b = b0 + blockIdx.y;
+  const double* src = (sel && ((sel[b] ^ flip) & 1)) ? a1 : a0;
+  double* fld = const_cast<double*>(src) + (size_t)b * per_problem;
+  double* usr = out + (size_t)blockIdx.y * per_problem;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < per_problem; e += (size_t)gridDim.x * blockDim.x) {
+    if (to_field)
+      fld[e] = usr[e];
+    else
+      usr[e] = fld[e];
+  }
+}
+
+}  // namespace cgx

@@ -11,6 +11,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
+from .arm import ArmActionModel, RevoluteChain, synthetic_arm  # noqa: F401
 from ._lib import CgxError, check, dptr, lib  # noqa: F401
 
 MODEL_LQR, MODEL_UNICYCLE, MODEL_ARM = 0, 1, 2

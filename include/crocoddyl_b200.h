@@ -72,7 +72,10 @@ CGX_API const char* cgx_version(void);
  *   params layout (doubles):
  *     LQR      [drift_free, Fx(n*n), Fu(n*m), f0(n), Lxx(n*n), Lxu(n*m), Luu(m*m), lx(n), lu(m)]
  *     UNICYCLE [dt, w_x, w_u]                                   (unicycle.hxx:14-15 defaults 0.1, 10, 1)
- *     ARM      see cgx_arm_param_count() / DESIGN.md "arm parameter block"
+ *     ARM      [dt, gravity(3), w_gripperPose, w_xReg, w_uReg, frame parent joint, frame placement R(9 row-major) p(3),
+ *               Mref R(9) p(3)] + per joint [axis(3), placement in parent R(9) p(3), mass, COM lever(3),
+ *               inertia about the COM Ixx Ixy Ixz Iyy Iyz Izz]  = cgx_arm_param_count(nv) = 32 + 25 nv doubles
+ *               (the model of benchmark/factory/arm.hpp:60-90; the terminal node is the same model with dt = 0)
  *   per_problem_params != 0: params holds B consecutive blocks of nparams doubles, else one shared block.
  *   x0s = [B][nx].
  */

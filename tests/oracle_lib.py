@@ -189,3 +189,15 @@ def lqr_params(n, m, drift_free=True, Fx=None, Fu=None, f0=None, Lxx=None, Lxu=N
 
 def unicycle_params(dt=0.1, wx=10.0, wu=1.0):
     return np.array([dt, wx, wu], dtype=np.float64)
+
+
+def arm_op(params, op, inp, nout):
+    """Rigid-body primitive of the arm oracle by name (oracle/arm.hpp arm_op)."""
+    lib = load(False)
+    params = np.ascontiguousarray(params, dtype=np.float64)
+    inp = np.ascontiguousarray(inp, dtype=np.float64)
+    out = np.zeros(nout)
+    n = lib.orc_arm_op(_p(params), params.size, op.encode(), _p(inp), _p(out))
+    if n < 0:
+        raise RuntimeError("orc_arm_op(%s) failed" % op)
+    return out[:n]

@@ -122,6 +122,7 @@ __device__ void cta_gemm(double* C, int ldc, const double* A, int lda, const dou
 // params = [drift_free, Fx(n*n), Fu(n*m), f0(n), Lxx(n*n), Lxu(n*m), Luu(m*m), lx(n), lu(m)], column-major.
 struct LqrModel {
   static constexpr bool kPerNodeMats = false;
+  static constexpr int kMinThreads = 64;
   const double *Fx, *Fu, *f0, *Lxx, *Lxu, *Luu, *lx, *lu;
   bool drift_free;
   int n, m;

@@ -2,6 +2,7 @@
 #include <cstring>
 #include "backend.hpp"
 #include "cta.cuh"
+#include "arm.cuh"
 
 namespace cgx {
 
@@ -34,7 +35,7 @@ struct CtaBackend : Backend {
     for (int i = 0; i < 4; ++i) CGX_CUDA(cudaEventCreate(&ev[i]));
     const int tn = (c.n + 3) / 4;
     threads = ((tn * tn + 31) / 32) * 32;
-    if (threads < 64) threads = 64;
+    if (threads < M::kMinThreads) threads = M::kMinThreads;
     if (threads > 384) threads = 384;
     smem = cta_smem_bytes(c.n, c.m);
     int dev = 0, maxsm = 0;
@@ -83,7 +84,7 @@ struct CtaBackend : Backend {
       c.d_Fx = alloc(B * (T + 1) * n * n);
       c.d_Fu = alloc(B * (T + 1) * n * m);
       c.d_Lxx = alloc(B * (T + 1) * n * n);
-      c.d_Lxu = alloc(B * (T + 1) * n * m);
+      c.d_Lxu = alloc(n * m);  // identically zero for the arm's cost set: one shared block
       c.d_Luu = alloc(B * (T + 1) * m * m);
     }
     data_allocated = true;
@@ -283,7 +284,17 @@ struct CtaBackend : Backend {
 
 Backend* make_cta_backend(const ProblemDesc* p, int solver_kind) {
   if (p->kind == 0) return new CtaBackend<LqrModel>(p, solver_kind);
-  throw Unsupported("CTA-per-problem backend: model kind not built yet");
+  if (p->kind == 2) {
+    switch (p->nu) {
+      case 2: return new CtaBackend<ArmModel<2> >(p, solver_kind);
+      case 4: return new CtaBackend<ArmModel<4> >(p, solver_kind);
+      case 7: return new CtaBackend<ArmModel<7> >(p, solver_kind);
+      default:
+        throw Unsupported("arm model: kernels are instantiated for nv = 2, 4 and 7 joints (got nv = " +
+                          std::to_string(p->nu) + ")");
+    }
+  }
+  throw Unsupported("CTA-per-problem backend: unknown model kind");
 }
 
 }  // namespace cgx

@@ -1,0 +1,179 @@
+"""GPU parity tests of the arm path (IntegratedActionModelEuler o DifferentialActionModelFreeFwdDynamics on a fixed-base
+revolute chain; BASELINE configs C4/C5) against the CPU oracle, through the C ABI. Patterns of the reference's tests:
+unittest/bindings/test_actions.py / test_shooting.py (calc, calcDiff, rollout of the C++ model vs a second statement),
+unittest/test_diff_actions.cpp:67-84 (quasiStatic => zero acceleration), unittest/bindings/test_solvers.py:99-144
+(FDDP on the Talos arm: step-wise Q*/V*/K/k, tryStep, expectedImprovement, solve). Tolerance 1e-9 relative."""
+import numpy as np
+import pytest
+
+import crocoddyl_b200 as cb
+import oracle_lib as ol
+from test_oracle_arm_cpu import _random_chain
+
+pytestmark = pytest.mark.gpu
+
+
+def _model(kind, nv, seed=0, **kw):
+    chain = cb.synthetic_arm(nv) if kind == "synthetic" else _random_chain(nv, seed)
+    return cb.ArmActionModel(chain, 1e-3, **kw)
+
+
+def _pair(solver_kind, model, x0, T):
+    problem = cb.ShootingProblem(x0, [model] * T, model.terminal_model)
+    solver = (cb.SolverFDDP if solver_kind == "fddp" else cb.SolverDDP)(problem)
+    ob = ol.OracleBatch("arm", solver_kind, T, model.nx, model.nu, model.params(), np.atleast_2d(x0))
+    return problem, solver, ob
+
+
+def _close(a, b, name, rtol=1e-9):
+    scale = max(1.0, float(np.max(np.abs(b))))
+    np.testing.assert_allclose(a, b, rtol=rtol, atol=rtol * scale, err_msg=name)
+
+
+def _c4_inputs(model, B, T, seed=2):
+    """q ~ U(-1,1)^nv, v = 0, init_xs = {x0}, init_us = quasiStatic(x0)."""
+    nv = model.nv
+    rng = np.random.default_rng(seed)
+    x0 = np.concatenate([rng.uniform(-1, 1, (B, nv)), np.zeros((B, nv))], 1)
+    return x0, np.repeat(x0[:, None, :], T + 1, 1)
+
+
+@pytest.mark.parametrize("kind,nv", [("synthetic", 7), ("random", 7), ("random", 4), ("random", 2)])
+def test_problem_calc_calcdiff_rollout_quasistatic(kind, nv):
+    model = _model(kind, nv, seed=4, w_xReg=1e-2, w_uReg=1e-3)
+    n, T, B = 2 * nv, 6, 5
+    rng = np.random.default_rng(nv)
+    x0 = np.concatenate([rng.uniform(-1.5, 1.5, (B, nv)), rng.standard_normal((B, nv))], 1)
+    problem, solver, ob = _pair("fddp", model, x0, T)
+    xs = np.concatenate([rng.uniform(-1.5, 1.5, (B, T + 1, nv)), rng.standard_normal((B, T + 1, nv))], 2)
+    us = 3. * rng.standard_normal((B, T, nv))
+    ob.set_candidate(xs, us, False)
+    _close(problem.calc(xs, us), ob.calc(), "total cost")
+    problem.calcDiff(xs, us)
+    ob.calcdiff()
+    for b in (0, B - 1):
+        for t in (0, T - 1, T):
+            for f in ("xnext", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu"):
+                if t == T and f in ("Lu", "Luu"):
+                    continue
+                _close(problem.data(f, b, t), ob.get(f, b, t), "%s b=%d t=%d" % (f, b, t))
+            _close(problem.data("cost", b, t), ob.get("node_cost", b, t), "node cost")
+    # quasiStatic: gravity torques; forward dynamics there gives zero acceleration (test_diff_actions.cpp:67-84)
+    xq = x0.copy()
+    xq[:, nv:] = 0.
+    uq = problem.quasiStatic(xq)
+    for b in range(B):
+        _close(uq[b], ol.arm_op(model.params(), "quasistatic", xq[b, :nv], nv), "quasiStatic")
+        a = ol.arm_op(model.params(), "aba", np.concatenate([xq[b], uq[b]]), nv)
+        assert np.max(np.abs(a)) <= 1e-8
+    # rollout (shooting.hxx:198-223): xs[t+1] = xnext(xs[t], us[t])
+    xr = problem.rollout(us)
+    np.testing.assert_allclose(xr[:, 0], x0)
+    ob.set_candidate(xr, us, True)
+    ob.calc()
+    for b in (0, B - 1):
+        for t in range(T):
+            _close(xr[b, t + 1], ob.get("xnext", b, t), "rollout")
+
+
+@pytest.mark.parametrize("solver_kind", ["ddp", "fddp"])
+@pytest.mark.parametrize("kind,nv,T", [("synthetic", 7, 12), ("random", 4, 9), ("random", 7, 5)])
+@pytest.mark.parametrize("feasible", [False, True])
+def test_stepwise_against_oracle(solver_kind, kind, nv, T, feasible):
+    model = _model(kind, nv, seed=T, w_xReg=1e-3, w_uReg=1e-3)
+    B = 4
+    rng = np.random.default_rng(100 + T)
+    x0 = np.concatenate([rng.uniform(-1, 1, (B, nv)), 0.5 * rng.standard_normal((B, nv))], 1)
+    problem, solver, ob = _pair(solver_kind, model, x0, T)
+    us = rng.standard_normal((B, T, nv))
+    if feasible:
+        xs = problem.rollout(us)
+    else:
+        xs = np.concatenate([rng.uniform(-1, 1, (B, T + 1, nv)), 0.5 * rng.standard_normal((B, T + 1, nv))], 2)
+    solver.setCandidate(xs, us, feasible)
+    ob.set_candidate(xs, us, feasible)
+    solver.x_reg = solver.u_reg = 1e-2
+    ob.set("xreg", 1e-2)
+    ob.set("ureg", 1e-2)
+    solver.computeDirection(True)
+    ob.calcdiff()
+    assert not ob.backward().any()
+    for name in ("fs", "Vxx", "Vx", "K", "k", "Qxx", "Qxu", "Quu", "Qx", "Qu"):
+        _close(solver.get(name), ob.get_all(name), name)
+    d_o, stop_o = ob.expected_improvement()
+    _close(solver.stoppingCriteria(), stop_o, "stop")
+    for alpha in (1.0, 0.5):
+        dV = solver.tryStep(alpha)
+        dV_o, st = ob.try_step(alpha)
+        assert not st.any()
+        cost_scale = max(1.0, float(np.max(np.abs(ob.scalars()["cost"]))))
+        np.testing.assert_allclose(dV, dV_o, rtol=1e-9, atol=1e-9 * cost_scale)
+        _close(solver.get("xs_try"), ob.get_all("xs_try"), "xs_try")
+        _close(solver.get("us_try"), ob.get_all("us_try"), "us_try")
+        d_o, _ = ob.expected_improvement()
+        _close(solver.expectedImprovement(), d_o, "d")
+
+
+def _compare_solve(solver, ob, conv, rtol=1e-9):
+    so, sg = ob.scalars(), solver.scalars()
+    assert np.array_equal(so["n_records"], sg["n_records"]), (so["n_records"], sg["n_records"])
+    assert np.array_equal(so["converged"].astype(bool), np.atleast_1d(conv))
+    assert np.array_equal(so["iter"], sg["iter"])
+    assert np.array_equal(so["is_feasible"], sg["is_feasible"])
+    for k in ("xreg", "ureg", "steplength"):
+        assert np.array_equal(so[k], sg[k]), k
+    _close(sg["cost"], so["cost"], "cost", rtol)
+    for name in ("xs", "us", "K", "k", "Vx", "Vxx"):
+        _close(solver.get(name), ob.get_all(name), name, rtol)
+
+
+@pytest.mark.parametrize("solver_kind", ["fddp", "ddp"])
+@pytest.mark.parametrize("kind,nv,T", [("synthetic", 7, 30), ("random", 4, 20)])
+def test_solve_same_iterations_and_accept_sequence(solver_kind, kind, nv, T):
+    model = _model(kind, nv, seed=9)
+    B = 6
+    x0, xs = _c4_inputs(model, B, T)
+    problem, solver, ob = _pair(solver_kind, model, x0, T)
+    us = np.repeat(problem.quasiStatic(x0)[:, None, :], T, 1)
+    solver.enableTrace(100)
+    conv = solver.solve(xs, us, 100, False, 0.1)  # reginit = 0.1 as benchmark/arm-manipulation-optctrl.cpp:61
+    ob.solve(xs, us, 100, False, 0.1)
+    # the iterates agree to ~1e-12 per iteration; over tens of iterations the comparison is made at 1e-7 on the
+    # trajectories (the discrete decisions below are compared exactly)
+    _compare_solve(solver, ob, conv, rtol=1e-7)
+    for b in range(B):
+        tg, to = solver.trace(b), ob.trace(b)
+        assert tg.shape == to.shape
+        for col in (0, 5, 6, 7, 8, 11, 12):  # iter, xreg, ureg, steplength, is_feasible, accepted alpha, retries
+            assert np.array_equal(tg[:, col], to[:, col]), (b, col)
+        np.testing.assert_allclose(tg[:, 1], to[:, 1], rtol=1e-9)  # cost per iteration
+
+
+def test_config_c4_full_horizon_sampled_against_oracle():
+    """BASELINE config C4 shape (7-DoF synthetic arm, T = 100, FDDP, reginit 0.1) on a batch, a sample of which is
+    solved by the oracle; plus size-independent properties on the whole batch."""
+    model = _model("synthetic", 7)
+    B, T, NS = 128, 100, 6
+    x0, xs = _c4_inputs(model, B, T)
+    problem = cb.ShootingProblem(x0, [model] * T, model.terminal_model)
+    solver = cb.SolverFDDP(problem)
+    solver.setStorage(False)
+    us = np.repeat(problem.quasiStatic(x0)[:, None, :], T, 1)
+    conv = solver.solve(xs, us, 100, False, 0.1)
+    sg = solver.scalars()
+    assert conv.mean() > 0.9
+    c = conv.astype(bool)
+    assert np.all(sg["is_feasible"][c] == 1) and np.all(sg["stop"][c] < 1e-9)
+    xg, ug = solver.get("xs"), solver.get("us")
+    np.testing.assert_allclose(xg[:, 0], x0, atol=1e-12)  # feasible => xs[0] = x0 and gaps closed
+    xr = problem.rollout(ug)
+    np.testing.assert_allclose(xr[c], xg[c], rtol=1e-9, atol=1e-9)
+    cost0 = problem.calc(xs, us)
+    assert np.all(sg["cost"][c] < cost0[c])
+    ob = ol.OracleBatch("arm", "fddp", T, 14, 7, model.params(), x0[:NS], fast=False)
+    ob.solve(xs[:NS], us[:NS], 100, False, 0.1)
+    so = ob.scalars()
+    assert np.array_equal(so["n_records"], sg["n_records"][:NS])
+    _close(sg["cost"][:NS], so["cost"], "cost")
+    _close(xg[:NS], ob.get_all("xs"), "xs", 1e-7)
+    _close(ug[:NS], ob.get_all("us"), "us", 1e-7)

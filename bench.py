@@ -1,9 +1,11 @@
 #!/usr/bin/env python
 """bench.py — FDDP OCP solves/s (batched, T=100) on B200, BASELINE.json's metric.
 
-Workload at every N: BASELINE config C2 per GPU — SolverFDDP on ActionModelUnicycle (nx=3, nu=2, T=100),
-65,536 random initial states per GPU (weak scaling: independent OCPs sharded over ranks, no data-path
-collective; one NCCL all-gather of {cost, iter, stop, converged} at the end of every step).
+Default workload at every N: BASELINE config C2 per GPU — SolverFDDP on ActionModelUnicycle (nx=3, nu=2, T=100),
+65,536 random initial states per GPU (weak scaling: independent OCPs sharded over ranks, no data-path collective;
+one NCCL all-gather of {cost, iter, stop, converged} at the end of every step).
+`--workload arm` runs configs C4/C5 instead: the synthetic 7-DoF arm (Euler o FreeFwdDynamics), B=1024 per GPU, or
+`--batch-total 8192` split contiguously over the ranks (strong scaling, config C5).
 A "step" = one batched solve() of all problems of the rank, run to each problem's own return.
 
   value : solves/s with init_xs/init_us already resident in HBM (cgx_solver_solve_resident), CUDA events on
@@ -14,7 +16,7 @@ A "step" = one batched solve() of all problems of the rank, run to each problem'
   cpu_baseline : the CPU oracle (restated reference algorithm, OpenMP over problems) on a bounded sample.
 
 `--impl reference` times the reference algorithm's CPU implementation (the oracle port; the reference itself
-cannot be compiled on this image — no Eigen/Boost) with all host threads on the same workload.
+cannot be compiled on this image — no Eigen/Boost/Pinocchio) with all host threads on the same workload.
 """
 import argparse
 import json
@@ -31,24 +33,80 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 T = 100
-B_PER_GPU = 65536
-NX, NU = 3, 2
 METRIC = "fddp_ocp_solves_per_sec_T100"
 UNIT = "solves/s"
-# algorithmic HBM bytes per node of the lean storage policy (DESIGN.md "bytes per node"): useful doubles only,
-# not the sector padding of the record layout
-NL = NX * (NX + 1) // 2
-BYTES_BWD_NODE = 8 * (NX + NU + NX + NU * NX + NU + NX + NX + NL)  # read xs,us ; write fs,K,k,w,Vx,tril(Vxx)
-BYTES_FWD_NODE = 8 * (NX + NU + NU * NX + NU + NX + NX + NX + NU)  # read xs,us,K,k,fs,w ; write xs_try,us_try
-BYTES_CALC_NODE = 8 * (NX + NU)
 
 
-def workload(rank, B):
-    rng = np.random.default_rng(1000 * rank)  # seed 0 on rank 0
-    x0 = np.stack([rng.uniform(-2, 2, B), rng.uniform(-2, 2, B), rng.uniform(-np.pi, np.pi, B)], 1)
-    xs = np.repeat(x0[:, None, :], T + 1, 1)
-    us = np.zeros((B, T, NU))
-    return x0, xs, us
+class Unicycle(object):
+    """BASELINE config C2: ActionModelUnicycle defaults, x0 ~ U([-2,2]^2 x [-pi,pi]), seed 0."""
+    name, nx, nu, reginit = "unicycle", 3, 2, 1e-9
+    default_batch, cpu_sample = 65536, 8192
+    kernel = "tpp_solve_kernel<UnicycleModel>"
+    oracle_kind = "unicycle"
+    # algorithmic HBM bytes per node of the lean storage policy (DESIGN.md): useful doubles only
+    bytes_bwd = 8 * (3 + 2 + 3 + 2 * 3 + 2 + 3 + 3 + 6)  # read xs,us ; write fs,K,k,w,Vx,tril(Vxx)
+    bytes_fwd = 8 * (3 + 2 + 2 * 3 + 2 + 3 + 3 + 3 + 2)  # read xs,us,K,k,fs,w ; write xs_try,us_try
+    bytes_calc = 8 * (3 + 2)
+
+    def describe(self, B):
+        return ("C2: SolverFDDP, ActionModelUnicycle nx=3 nu=2 T=100, %d random x0 per GPU, init_xs={x0}x101, "
+                "init_us=0, maxiter=100, reginit=1e-9" % B)
+
+    def model(self):
+        import crocoddyl_b200 as cb
+
+        return cb.ActionModelUnicycle()
+
+    def terminal(self, model):
+        return model
+
+    def oracle_params(self):
+        import oracle_lib as ol
+
+        return ol.unicycle_params()
+
+    def inputs(self, lo, hi, total, seed):
+        rng = np.random.default_rng(seed)
+        x0 = np.stack([rng.uniform(-2, 2, total), rng.uniform(-2, 2, total), rng.uniform(-np.pi, np.pi, total)], 1)[lo:hi]
+        return x0, np.repeat(x0[:, None, :], T + 1, 1), np.zeros((hi - lo, T, 2))
+
+
+class Arm(object):
+    """BASELINE configs C4/C5: synthetic 7-DoF arm, Euler(1e-3) o FreeFwdDynamics, costs gripperPose 1,
+    xReg 1e-4, uReg 1e-4; q ~ U(-1,1)^7, v = 0, seed 2; init_us = quasiStatic(x0); reginit 0.1."""
+    name, nx, nu, reginit = "arm", 14, 7, 0.1
+    default_batch, cpu_sample = 1024, 256
+    kernel = "cta_solve_kernel<ArmModel<7>>"
+    oracle_kind = "arm"
+    n, m = 14, 7
+    # CTA-per-problem core: node derivatives are written by calcDiff and read back by the backward pass
+    bytes_bwd = 8 * ((n + m) + 2 * (2 * n * n + n * m + m * m + n + m) + n + m * n + m + 2 * n + n * n)
+    bytes_fwd = 8 * (n + m + m * n + m + n + n + n + m + n + 1)
+    bytes_calc = 8 * (n + m + n + 1)
+
+    def describe(self, B):
+        return ("C4/C5: SolverFDDP, 7-DoF synthetic arm (IntegratedActionModelEuler dt=1e-3 o DifferentialActionModel"
+                "FreeFwdDynamics, gripperPose+xReg+uReg), nx=14 nu=7 T=100, %d random q0 per GPU, init_xs={x0}x101, "
+                "init_us=quasiStatic(x0), maxiter=100, reginit=0.1" % B)
+
+    def model(self):
+        import crocoddyl_b200 as cb
+
+        return cb.ArmActionModel(cb.synthetic_arm(7), 1e-3, w_gripperPose=1., w_xReg=1e-4, w_uReg=1e-4)
+
+    def terminal(self, model):
+        return model.terminal_model
+
+    def oracle_params(self):
+        return self.model().params()
+
+    def inputs(self, lo, hi, total, seed):
+        rng = np.random.default_rng(2 + seed)
+        x0 = np.concatenate([rng.uniform(-1, 1, (total, 7)), np.zeros((total, 7))], 1)[lo:hi]
+        return x0, np.repeat(x0[:, None, :], T + 1, 1), None  # us = quasiStatic(x0), filled by the caller
+
+
+WORKLOADS = {"unicycle": Unicycle, "arm": Arm}
 
 
 class ClockSampler(object):
@@ -107,49 +165,59 @@ def hbm_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def cpu_oracle_rate(nsample, nthreads=0, reps=1):
+def oracle_inputs(wl, nsample):
+    """First nsample problems of rank 0's workload, for the CPU legs."""
+    import oracle_lib as ol
+
+    x0, xs, us = wl.inputs(0, nsample, max(nsample, wl.default_batch), 0)
+    params = wl.oracle_params()
+    if us is None:
+        u0 = np.stack([ol.arm_op(params, "quasistatic", x0[b, :wl.nu], wl.nu) for b in range(nsample)])
+        us = np.repeat(u0[:, None, :], T, 1)
+    return params, x0, xs, us
+
+
+def cpu_oracle_rate(wl, nsample, nthreads=0, reps=1):
     """Reference algorithm on the host cores: oracle, -O3 build, OpenMP over problems."""
     import oracle_lib as ol
 
-    x0, xs, us = workload(0, B_PER_GPU)
-    x0, xs, us = x0[:nsample], xs[:nsample], us[:nsample]
-    ob = ol.OracleBatch("unicycle", "fddp", T, NX, NU, ol.unicycle_params(), x0, fast=True)
+    params, x0, xs, us = oracle_inputs(wl, nsample)
+    ob = ol.OracleBatch(wl.oracle_kind, "fddp", T, wl.nx, wl.nu, params, x0, fast=True)
     best = None
     for _ in range(reps):
-        ob.solve(xs, us, 100, False, 1e-9, nthreads=nthreads)
+        ob.solve(xs, us, 100, False, wl.reginit, nthreads=nthreads)
         best = ob.seconds if best is None else min(best, ob.seconds)
     cores = ob.lib.orc_max_threads() if nthreads <= 0 else nthreads
     return nsample / best, cores, best
 
 
-def run_reference(args, rank, world):
+def run_reference(args, wl, rank, world):
     if rank != 0:
         return
     import __graft_entry__ as ge
 
     ge.build(quiet=True)
-    nsample = 8192
-    times = []
     import oracle_lib as ol
 
-    x0, xs, us = workload(0, B_PER_GPU)
-    x0, xs, us = x0[:nsample], xs[:nsample], us[:nsample]
-    ob = ol.OracleBatch("unicycle", "fddp", T, NX, NU, ol.unicycle_params(), x0, fast=True)
+    nsample = wl.cpu_sample
+    params, x0, xs, us = oracle_inputs(wl, nsample)
+    ob = ol.OracleBatch(wl.oracle_kind, "fddp", T, wl.nx, wl.nu, params, x0, fast=True)
     cores = ob.lib.orc_max_threads()
+    times = []
     for i in range(args.warmup + args.steps):
-        ob.solve(xs, us, 100, False, 1e-9, nthreads=0)
+        ob.solve(xs, us, 100, False, wl.reginit, nthreads=0)
         if i >= args.warmup:
             times.append(ob.seconds)
     tot = sum(times)
     value = nsample * len(times) / tot
-    sample = "first %d of the %d problems of config C2 per step (same seeds), OpenMP over problems" % (nsample, B_PER_GPU)
+    sample = "first %d problems of the workload per step (same seeds), OpenMP over problems, %d threads" % (nsample, cores)
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "C2: SolverFDDP, ActionModelUnicycle nx=3 nu=2 T=100, random x0, maxiter=100",
-                   "problems_per_step": nsample, "note": "CPU port of the reference algorithm (oracle/); the reference "
-                   "itself needs Eigen+Boost which this image lacks"},
+        "config": {"workload": wl.describe(nsample), "problems_per_step": nsample,
+                   "note": "CPU port of the reference algorithm (oracle/, -O3, OpenMP over problems); the reference itself "
+                           "needs Eigen+Boost(+Pinocchio), which this image lacks"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -162,15 +230,20 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--batch", type=int, default=B_PER_GPU)
+    ap.add_argument("--workload", default="unicycle", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="problems per GPU (weak scaling)")
+    ap.add_argument("--batch-total", type=int, default=0, help="total problems split over the ranks (strong scaling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    wl = WORKLOADS[args.workload]()
     if args.impl == "reference":
-        run_reference(args, rank, world)
+        run_reference(args, wl, rank, world)
         return
+
+    import ctypes as C
 
     import torch
     import __graft_entry__ as ge
@@ -185,47 +258,53 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         dist.barrier()
     import crocoddyl_b200 as cb
+    from crocoddyl_b200 import sharding
 
     cb.set_device(local_rank)
     torch.cuda.set_device(local_rank)
-    B = args.batch
-    x0, xs_np, us_np = workload(rank, B)
+    if args.batch_total:  # strong scaling: one global batch, contiguous shards
+        total, scaling = args.batch_total, "strong"
+        lo, hi = sharding.shard_range(total, rank, world)
+        x0, xs_np, us_np = wl.inputs(lo, hi, total, 0)
+    else:  # weak scaling: the same per-GPU batch on every rank, different seeds
+        B0 = args.batch or wl.default_batch
+        total, scaling = B0 * world, "weak"
+        lo, hi = rank * B0, (rank + 1) * B0
+        x0, xs_np, us_np = wl.inputs(0, B0, B0, 1000 * rank)
+    B = hi - lo
+    model = wl.model()
+    problem = cb.ShootingProblem(x0, [model] * T, wl.terminal(model))
+    if us_np is None:
+        us_np = np.repeat(problem.quasiStatic(x0)[:, None, :], T, 1)
     # pinned host buffers (what a caller hands to the reference-facing API)
-    xs_h = torch.from_numpy(xs_np).pin_memory()
-    us_h = torch.from_numpy(us_np).pin_memory()
+    xs_h = torch.from_numpy(np.ascontiguousarray(xs_np)).pin_memory()
+    us_h = torch.from_numpy(np.ascontiguousarray(us_np)).pin_memory()
     xs_out = torch.empty_like(xs_h).pin_memory()
     us_out = torch.empty_like(us_h).pin_memory()
-    model = cb.ActionModelUnicycle()
-    problem = cb.ShootingProblem(x0, [model] * T, model)
     solver = cb.SolverFDDP(problem)
     solver.setStorage(False)  # lean: keeps xs, us, K, k, Vx, Vxx, fs (the accessors north_star names)
     L = cb.lib()
     h = solver._h
     conv = np.zeros(B, dtype=np.uint8)
     scal = np.zeros((B, 17))
-    import ctypes as C
+    dev = torch.device("cuda", local_rank)
 
     def dp(t):
         return C.cast(t.data_ptr(), C.POINTER(C.c_double))
 
     def gather_results():
         # the one collective of the path: per-problem {cost, iter, stop, converged} to every rank
-        if dist is None:
-            return None
-        rec = torch.from_numpy(np.ascontiguousarray(scal[:, [0, 9, 1, 11]])).cuda()
-        out = torch.empty((world,) + tuple(rec.shape), dtype=rec.dtype, device=rec.device)
-        dist.all_gather_into_tensor(out, rec)
-        return out
+        return sharding.gather_records(sharding.records_from_scalars(scal), total, dist, dev)
 
     def step_resident():
-        cb.check(L.cgx_solver_solve_resident(h, 100, 0, 1e-9))
+        cb.check(L.cgx_solver_solve_resident(h, 100, 0, wl.reginit))
         cb.check(L.cgx_solver_download(h, conv.ctypes.data_as(C.POINTER(C.c_ubyte))))
         cb.check(L.cgx_solver_get_scalars(h, cb.dptr(scal)))
         gather_results()
         return solver.timing()
 
     def step_e2e():
-        cb.check(L.cgx_solver_solve(h, dp(xs_h), dp(us_h), 100, 0, 1e-9, conv.ctypes.data_as(C.POINTER(C.c_ubyte))))
+        cb.check(L.cgx_solver_solve(h, dp(xs_h), dp(us_h), 100, 0, wl.reginit, conv.ctypes.data_as(C.POINTER(C.c_ubyte))))
         cb.check(L.cgx_solver_get_all(h, b"xs", dp(xs_out)))
         cb.check(L.cgx_solver_get_all(h, b"us", dp(us_out)))
         cb.check(L.cgx_solver_get_scalars(h, cb.dptr(scal)))
@@ -258,7 +337,8 @@ def main():
     dev_ms = float(np.sum(call_ms))
     sg = solver.scalars()
     nb, nf = sg["n_backward"], sg["n_forward"]
-    alg_bytes = float(T * (nb * BYTES_BWD_NODE + (nf - 1) * BYTES_FWD_NODE + BYTES_CALC_NODE).sum())
+    alg_bytes = float(T * (nb * wl.bytes_bwd + (nf - 1) * wl.bytes_fwd + wl.bytes_calc).sum())
+    records = gather_results()
     # ---- e2e ---------------------------------------------------------------------------------
     for _ in range(2):
         step_e2e()
@@ -273,42 +353,43 @@ def main():
         dist.all_reduce(v, op=dist.ReduceOp.MAX)
         dev_ms, e2e_ms, wall_ms = [float(a) for a in v.cpu()]
     if rank == 0:
-        total = B * world * args.steps
-        value = total / (dev_ms * 1e-3)
+        solved = total * args.steps
+        value = solved / (dev_ms * 1e-3)
         peak, peak_src = hbm_peak()
         kms = float(np.mean(kern_ms))
         achieved = alg_bytes / (kms * 1e-3) / 1e9
         h2d = int(xs_h.numel() * 8 + us_h.numel() * 8)
         d2h = int(xs_out.numel() * 8 + us_out.numel() * 8 + scal.size * 8 * 2 + B)
+        ws_gb = (2 * xs_h.numel() + 2 * us_h.numel()) * 8 / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": scaling,
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "C2: SolverFDDP, ActionModelUnicycle nx=3 nu=2 T=100, %d random x0 per GPU, "
-                       "init_xs={x0}x101, init_us=0, maxiter=100, reginit=1e-9" % B,
-                       "problems_per_gpu": B, "storage": "lean (xs,us,K,k,Vx,Vxx,fs kept)",
-                       "l2": "working set 1.9 GB per GPU >> 126 MB L2 (inputs larger than L2)",
+            "config": {"workload": wl.describe(B), "problems_per_gpu": B, "problems_total": total,
+                       "storage": "lean (xs,us,K,k,Vx,Vxx,fs kept)",
+                       "l2": "inputs larger than L2: trajectories alone are %.2f GB per GPU; every step rewrites the whole "
+                             "solver state" % ws_gb,
                        "parallelism": "independent OCPs sharded over %d rank(s); NCCL all-gather of per-problem "
                        "{cost,iter,stop,converged}" % world},
-            "e2e": {"value": total / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "e2e": {"value": solved / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "wall_ms_per_step": wall_ms / args.steps,
-            "solve_stats": {"iterations_mean": float(sg["n_records"].mean()), "converged_frac": float(conv.mean()),
+            "solve_stats": {"iterations_mean": float(records[:, 1].mean()), "converged_frac": float(records[:, 3].mean()),
                             "backward_sweeps_mean": float(nb.mean()), "forward_sweeps_mean": float(nf.mean())},
-            "roofline": {"kernel": "tpp_solve_kernel<UnicycleModel>", "bound": "hbm", "achieved": achieved, "peak": peak,
+            "roofline": {"kernel": wl.kernel, "bound": "hbm", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": kms},
         }
         if not args.no_cpu_baseline:
-            nsample = 8192
-            rate, cores, sec = cpu_oracle_rate(nsample)
+            nsample = wl.cpu_sample
+            rate, cores, sec = cpu_oracle_rate(wl, nsample)
             line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": "first %d problems of the same workload, %.2f s, OpenMP over problems" %
                                     (nsample, sec)}
         prof = os.path.join(ROOT, "profiles", "traffic_r01.json")
-        if os.path.exists(prof):
+        if os.path.exists(prof) and wl.name == "unicycle" and B == 65536:
             try:
                 line["roofline"]["traffic"] = json.load(open(prof)).get("tpp_solve_kernel_dram_bytes_per_launch")
             except Exception:

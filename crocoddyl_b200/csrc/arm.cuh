@@ -13,6 +13,10 @@
 #include "cta.cuh"
 #include "rigid_body.cuh"
 
+#ifndef CGX_ARM_MINBLOCKS
+#define CGX_ARM_MINBLOCKS 4
+#endif
+
 namespace cgx {
 
 template <int NV>
@@ -41,7 +45,9 @@ __global__ void arm_quasi_static_kernel(const double* params, long nparams, int 
 template <int NV>
 struct ArmModel {
   static constexpr bool kPerNodeMats = true;
-  static constexpr int kMinThreads = 128;
+  // the solve kernel is latency-bound (serial recursions over joints and nodes): resident blocks per SM matter more
+  // than registers per thread, so the register file is split over CGX_ARM_MINBLOCKS blocks of 128 threads
+  static constexpr int kMinThreads = 128, kMaxThreads = 128, kMinBlocks = CGX_ARM_MINBLOCKS;
   const double* params;
 
   // host side: device address of a derivative matrix of node t of problem b

@@ -122,7 +122,7 @@ __device__ void cta_gemm(double* C, int ldc, const double* A, int lda, const dou
 // params = [drift_free, Fx(n*n), Fu(n*m), f0(n), Lxx(n*n), Lxu(n*m), Luu(m*m), lx(n), lu(m)], column-major.
 struct LqrModel {
   static constexpr bool kPerNodeMats = false;
-  static constexpr int kMinThreads = 64;
+  static constexpr int kMinThreads = 64, kMaxThreads = 384, kMinBlocks = 1;
   const double *Fx, *Fu, *f0, *Lxx, *Lxu, *Luu, *lx, *lu;
   bool drift_free;
   int n, m;
@@ -656,7 +656,7 @@ __device__ inline bool cta_accept(const SolverOpts& o, bool fddp, bool is_feasib
 // Whole SolverDDP::solve / SolverFDDP::solve loop for one problem per block (ddp.cpp:41-118, fddp.cpp:19-105).
 // All control-flow variables are block-uniform (every thread computes the same scalars from broadcast values).
 template <class M>
-__global__ void cta_solve_kernel(const __grid_constant__ CtaCtx c, int maxiter, int is_feasible0, double reginit) {
+__global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_solve_kernel(const __grid_constant__ CtaCtx c, int maxiter, int is_feasible0, double reginit) {
   extern __shared__ double cta_smem_raw[];
   const int b = blockIdx.x;
   CtaSmem sm;

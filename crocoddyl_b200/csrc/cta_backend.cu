@@ -36,7 +36,7 @@ struct CtaBackend : Backend {
     const int tn = (c.n + 3) / 4;
     threads = ((tn * tn + 31) / 32) * 32;
     if (threads < M::kMinThreads) threads = M::kMinThreads;
-    if (threads > 384) threads = 384;
+    if (threads > M::kMaxThreads) threads = M::kMaxThreads;
     smem = cta_smem_bytes(c.n, c.m);
     int dev = 0, maxsm = 0;
     CGX_CUDA(cudaGetDevice(&dev));

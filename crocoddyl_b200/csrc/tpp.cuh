@@ -175,7 +175,9 @@ struct UnicycleModel {
 #else
 #define TPP_SWEEP_ATTR __device__ __forceinline__
 #endif
+#ifndef TPP_PF_DIST
 #define TPP_PF_DIST 3  // L2 prefetch distance in nodes (the register prefetch is one node ahead)
+#endif
 #define TPP_REC(base, t, R) ((base) + ((size_t)(t) * (size_t)Bp + b) * (R))
 
 // ---------------------------------------------------------------------------------------------
@@ -633,10 +635,17 @@ __device__ inline bool accept_step(const SolverOpts& o, bool fddp, bool is_feasi
 
 // ---------------------------------------------------------------------------------------------
 // Whole SolverDDP::solve / SolverFDDP::solve loop for one problem per thread (ddp.cpp:41-118, fddp.cpp:19-105).
+// The loop is RESUMABLE: a launch runs at most `chunk` iterations of every problem it owns (chunk <= 0: all of them),
+// saves the loop state in the per-problem slots and sets I_FINISHED when solve() has returned. Between launches the
+// host compacts the unfinished problems into `list` (tpp_compact_*), so that a launch only spends lanes on OCPs that
+// still iterate: each OCP has its own iteration count, and without compaction one slow lane keeps its whole warp
+// alive (ncu, profiles/README.md: 19 % of the warp slots active at B = 65,536).
 template <class M>
-__global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, int is_feasible0, double reginit) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= c.B) return;
+__global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, int is_feasible0, double reginit, int chunk,
+                                 int first, const int* __restrict__ list, const int* __restrict__ nactive) {
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (list ? *nactive : c.B)) return;
+  const int b = list ? list[gid] : gid;
   const int Bp = c.Bp;
   const bool fddp = c.fddp != 0;
   M m;
@@ -649,7 +658,28 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
   double dg = 0., dq = 0.;
   int nbwd = 0, nfwd = 0, nrec = 0, converged = 0, iter = 0;
   bool recalc = true, need_gaps = true, done = false;
-  for (iter = 0; iter < maxiter && !done; ++iter) {
+  if (!first) {  // resume
+    feas = TPP_I(I_FEAS) != 0;
+    wasfeas = TPP_I(I_WASFEAS) != 0;
+    xreg = TPP_S(S_XREG);
+    ureg = TPP_S(S_UREG);
+    dg = TPP_S(S_DG);
+    dq = TPP_S(S_DQ);
+    nbwd = TPP_I(I_NBWD);
+    nfwd = TPP_I(I_NFWD);
+    nrec = TPP_I(I_NREC);
+    iter = TPP_I(I_ITER);
+    const int lp = TPP_I(I_LOOP);
+    recalc = (lp & 1) != 0;
+    need_gaps = (lp & 2) != 0;
+  }
+  int budget = chunk > 0 ? chunk : maxiter + 1;
+  bool paused = false;
+  for (; iter < maxiter && !done; ++iter) {
+    if (budget-- == 0) {
+      paused = true;
+      break;
+    }
     int retries = 0;
     if (recalc && iter == 0) {  // ddp.cpp:158
       cost = tpp_calc_pass(c, m, b, c.xu[cur]);
@@ -749,6 +779,45 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
   TPP_I(I_NREC) = nrec;
   TPP_I(I_NBWD) = nbwd;
   TPP_I(I_NFWD) = nfwd;
+  TPP_I(I_LOOP) = (recalc ? 1 : 0) | (need_gaps ? 2 : 0);
+  TPP_I(I_FINISHED) = paused ? 0 : 1;
+}
+
+// Ordered compaction of the unfinished problems (keeps neighbouring OCPs in neighbouring lanes):
+//   pass 1: counts[blk] = unfinished problems among the 1024 of block blk
+//   pass 2: list[prefix(blk) + rank in block] = b ; nactive = total
+__global__ void __launch_bounds__(1024) tpp_compact_count_kernel(const int* __restrict__ finished, int B, int* counts) {
+  const int b = blockIdx.x * 1024 + threadIdx.x;
+  const int act = (b < B && finished[b] == 0) ? 1 : 0;
+  const int n = __syncthreads_count(act);
+  if (threadIdx.x == 0) counts[blockIdx.x] = n;
+}
+__global__ void __launch_bounds__(1024) tpp_compact_scatter_kernel(const int* __restrict__ finished, int B,
+                                                                   const int* __restrict__ counts, int* list, int* nactive) {
+  __shared__ int warp_off[32];
+  __shared__ int base;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int b = blockIdx.x * 1024 + tid;
+  const int act = (b < B && finished[b] == 0) ? 1 : 0;
+  const unsigned bal = __ballot_sync(0xffffffffu, act);
+  if (lane == 0) warp_off[wid] = __popc(bal);
+  if (tid == 0) {
+    int s = 0;
+    for (int i = 0; i < (int)blockIdx.x; ++i) s += counts[i];
+    base = s;
+    if (blockIdx.x == gridDim.x - 1) *nactive = s + counts[blockIdx.x];
+  }
+  __syncthreads();
+  if (wid == 0) {  // exclusive scan of the 32 warp counts
+    int v = warp_off[lane], x = v;
+    for (int d = 1; d < 32; d <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, d);
+      if (lane >= d) x += y;
+    }
+    warp_off[lane] = x - v;
+  }
+  __syncthreads();
+  if (act) list[base + warp_off[wid] + __popc(bal & ((1u << lane) - 1u))] = b;
 }
 
 // ---------------------------------------------------------------------------------------------

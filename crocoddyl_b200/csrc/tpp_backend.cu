@@ -1,6 +1,7 @@
 // crocoddyl_b200 — host driver of the thread-per-problem kernels (tpp.cuh). Model family: unicycle.
 #include <cstring>
 #include <map>
+#include <cstdlib>
 #include "backend.hpp"
 #include "tpp.cuh"
 
@@ -14,6 +15,7 @@ struct TppBackend : Backend {
   TppCtx c;
   std::vector<void*> allocs;
   bool solver_allocated = false;
+  int* d_list = nullptr;  // compaction: [Bp] problem indices, per-block counts, number of unfinished problems
   double* node_data[9] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
   explicit TppBackend(const ProblemDesc* p_, int sk) {
@@ -113,12 +115,41 @@ struct TppBackend : Backend {
     if (d_us) gather(const_cast<double*>(d_us), fmap("us"), c.xu[0], c.xu[0], nullptr, 0, 0, c.B, 1);
   }
 
+  // Optional chunked solve: `chunk` iterations per launch, unfinished problems compacted in between (tpp.cuh).
+  // MEASURED on B200 (config C2, B = 65,536, profiles/README.md): one launch 51.1 ms; chunk 8 / 4 / 2 = 53.9 / 58.0 /
+  // 65.5 ms. The loop is bound by the dependent instruction chain of each OCP (0.3 ms per iteration for a lone warp)
+  // and by instruction issue while all OCPs are alive, not by idle lanes, and compaction scatters the lanes' records
+  // over DRAM pages. So the default stays ONE launch (0); CROCODDYL_B200_TPP_CHUNK=<n> enables the chunked path.
+  int chunk_iters() const {
+    const char* e = getenv("CROCODDYL_B200_TPP_CHUNK");
+    return e ? atoi(e) : 0;
+  }
   void solve(int maxiter, int is_feasible, double reginit) override {
     c.o = o;
+    const int chunk = chunk_iters();
     CGX_CUDA(cudaEventRecord(ev[1], stream));
-    tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit);
+    if (chunk <= 0 || maxiter <= chunk) {
+      tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr);
+      ++last_launches;
+    } else {
+      const int cblocks = (c.B + 1023) / 1024;
+      if (!d_list) {
+        d_list = dalloc<int>((size_t)c.Bp + cblocks + 1);
+        allocs.push_back(d_list);
+      }
+      int* d_counts = d_list + c.Bp;
+      int* d_nactive = d_counts + cblocks;
+      const int* fin = c.iscal + (size_t)I_FINISHED * c.Bp;
+      tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit, chunk, 1, nullptr, nullptr);
+      ++last_launches;
+      for (int done = chunk; done < maxiter; done += chunk) {
+        tpp_compact_count_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts);
+        tpp_compact_scatter_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts, d_list, d_nactive);
+        tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit, chunk, 0, d_list, d_nactive);
+        last_launches += 3;
+      }
+    }
     CGX_CUDA(cudaEventRecord(ev[2], stream));
-    ++last_launches;
     CGX_CUDA(cudaGetLastError());
   }
   void compute_direction(int recalc) override {

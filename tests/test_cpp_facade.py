@@ -1,0 +1,59 @@
+"""C++ facade (include/crocoddyl_b200.hpp) over the C ABI: compiles with g++, refuses to run without a GPU (no CPU
+fallback), and on a GPU reproduces the oracle's FDDP solve of the benchmark/unicycle-optctrl.cpp problem."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import crocoddyl_b200 as cb
+import oracle_lib as ol
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _build():
+    out_dir = os.path.join(ROOT, "tests", "cpp", "_build")
+    os.makedirs(out_dir, exist_ok=True)
+    exe = os.path.join(out_dir, "facade_demo")
+    src = os.path.join(ROOT, "tests", "cpp", "facade_demo.cpp")
+    lib = cb._lib.LIB_PATH
+    cb.lib()  # builds / loads the library
+    deps = [src, os.path.join(ROOT, "include", "crocoddyl_b200.hpp"), os.path.join(ROOT, "include", "crocoddyl_b200.h")]
+    if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(d) for d in deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O1", "-I", os.path.join(ROOT, "include"), src, "-o", exe,
+                               "-L", os.path.dirname(lib), "-lcrocoddyl_b200", "-Wl,-rpath," + os.path.dirname(lib)])
+    return exe
+
+
+def test_facade_compiles_and_refuses_without_gpu():
+    exe = _build()
+    if cb.device_count() > 0:
+        pytest.skip("a GPU is present: covered by the gpu test")
+    r = subprocess.run([exe, "10"], stdout=subprocess.PIPE, text=True)
+    assert r.returncode == 3, r.stdout
+    assert "no CUDA device" in r.stdout or "CUDA" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,T", [("unicycle", 20), ("lqr", 15)])
+def test_facade_solve_matches_oracle(kind, T):
+    exe = _build()
+    r = subprocess.run([exe, str(T)] + (["lqr"] if kind == "lqr" else []), stdout=subprocess.PIPE, text=True)
+    assert r.returncode == 0, r.stdout
+    lines = r.stdout.strip().split("\n")
+    head = lines[0].split()
+    vals = {ln.split()[0]: np.array([float(v) for v in ln.split()[1:]]) for ln in lines[1:4]}
+    if kind == "unicycle":
+        nx, nu, params, x0 = 3, 2, ol.unicycle_params(), np.array([[-1., -1., 1.]])
+    else:
+        nx, nu, params, x0 = 6, 2, ol.lqr_params(6, 2), np.zeros((1, 6))
+    ob = ol.OracleBatch(kind, "fddp", T, nx, nu, params, x0)
+    ob.solve(np.repeat(x0[:, None, :], T + 1, 1), np.zeros((1, T, nu)), 100, False, 1e-9)
+    so = ob.scalars()
+    assert int(head[1]) == int(so["converged"][0]) and int(head[3]) == int(so["iter"][0])
+    np.testing.assert_allclose(float(head[5]), so["cost"][0], rtol=1e-9)
+    np.testing.assert_allclose(vals["xs"], ob.get_all("xs").ravel(), rtol=1e-9, atol=1e-9)
+    np.testing.assert_allclose(vals["us"], ob.get_all("us").ravel(), rtol=1e-9, atol=1e-9)
+    np.testing.assert_allclose(vals["K0"], ob.get("K", 0, 0).ravel(order="F"), rtol=1e-9, atol=1e-9)
+    assert "Warm start state has wrong dimension" in lines[4]

@@ -12,6 +12,7 @@
 #pragma once
 #include "cta.cuh"
 #include "rigid_body.cuh"
+#include "arm_warp.cuh"
 
 #ifndef CGX_ARM_MINBLOCKS
 #define CGX_ARM_MINBLOCKS 4
@@ -48,6 +49,7 @@ struct ArmModel {
   // the solve kernel is latency-bound (serial recursions over joints and nodes): resident blocks per SM matter more
   // than registers per thread, so the register file is split over CGX_ARM_MINBLOCKS blocks of 128 threads
   static constexpr int kMinThreads = 128, kMaxThreads = 128, kMinBlocks = CGX_ARM_MINBLOCKS;
+  static constexpr int kN = 2 * NV, kM = NV;  // compile-time node sizes for the warp-level backward pass
   const double* params;
 
   // host side: device address of a derivative matrix of node t of problem b
@@ -103,20 +105,11 @@ struct ArmModel {
                                 c.d_Lx + node * n, c.d_Lu + node * m, c.d_Lxx + node * n * n, c.d_Luu + node * m * m);
     }
   }
-  // calc of one node for the rollout: x, u (null at the terminal node) and xnext in shared memory
+  // calc of one node for the rollout: x, u (null at the terminal node) and xnext in shared memory; warp 0 evaluates
+  // it cooperatively (arm_warp.cuh), the other warps of the block wait
   __device__ void calc_block(const double* x, const double* u, double* xnext, double*, double* cost_out) const {
-    if (threadIdx.x == 0) {
-      double xl[2 * NV], ul[NV], xn[2 * NV];
-#pragma unroll
-      for (int i = 0; i < 2 * NV; ++i) xl[i] = x[i];
-      if (u) {
-#pragma unroll
-        for (int i = 0; i < NV; ++i) ul[i] = u[i];
-      }
-      *cost_out = arm_calc_node_dev<NV>(params, u == nullptr, xl, u ? ul : nullptr, xn);
-#pragma unroll
-      for (int i = 0; i < 2 * NV; ++i) xnext[i] = xn[i];
-    }
+    __shared__ ArmWarpSmem<NV> W;
+    if (threadIdx.x < 32) arm_calc_warp<NV>(params, u == nullptr, x, u, xnext, cost_out, W);
     __syncthreads();
   }
 };

@@ -67,6 +67,10 @@ struct NodeMats {
   bool constant;  // the same for every running node of the problem (LQR): stage once
 };
 
+}  // namespace cgx
+#include "cta_small.cuh"
+namespace cgx {
+
 __device__ __forceinline__ int cta_ld(int rows) { return rows | 1; }  // odd leading dimension: no bank conflicts
 
 // ---------------------------------------------------------------------------------------------
@@ -123,6 +127,7 @@ __device__ void cta_gemm(double* C, int ldc, const double* A, int lda, const dou
 struct LqrModel {
   static constexpr bool kPerNodeMats = false;
   static constexpr int kMinThreads = 64, kMaxThreads = 384, kMinBlocks = 1;
+  static constexpr int kN = 0, kM = 0;  // run-time sizes
   const double *Fx, *Fu, *f0, *Lxx, *Lxu, *Luu, *lx, *lu;
   bool drift_free;
   int n, m;
@@ -305,7 +310,9 @@ struct CtaSmem {
 };
 inline size_t cta_smem_bytes(int n, int m) {
   const size_t ldn = n | 1, ldm = (m | 1);
-  return 8 * (3 * ldn * n + 2 * ldn * m + 2 * ldm * n + 2 * ldm * m + 6 * (size_t)n + 4 * (size_t)m + (2 * n + m) + 16);
+  const size_t blockwide = 8 * (3 * ldn * n + 2 * ldn * m + 2 * ldm * n + 2 * ldm * m + 6 * (size_t)n + 4 * (size_t)m + (2 * n + m) + 16);
+  const size_t warpwide = cta_is_small(n, m) ? cta_small_smem_bytes(n, m) : 0;  // the two plans overlay each other
+  return blockwide > warpwide ? blockwide : warpwide;
 }
 
 // copy a column-major rows x cols matrix from global memory to shared memory (leading dim ld)
@@ -355,6 +362,9 @@ __device__ double cta_calcdiff(const CtaCtx& c, const M& mod, CtaSmem& sm, int b
 template <class M>
 __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, bool is_feasible, double xreg,
                             double ureg, double& dg_out, double& dq_out, double& stop_out) {
+#ifndef CGX_NO_SMALL_BACKWARD
+  if (cta_is_small(c.n, c.m)) return cta_backward_warp<M::kN, M::kM>(c, mod, b, is_feasible, xreg, ureg, dg_out, dq_out, stop_out);
+#endif
   const int T = c.T, n = c.n, m = c.m, ldn = sm.ldn, ldm = sm.ldm;
   const int tid = threadIdx.x, P = blockDim.x;
   const bool fddp = c.fddp != 0, full = c.full != 0;
@@ -772,7 +782,7 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_solve_kerne
 // Step-wise kernels. what: 0 = calcDiff only, 1 = backwardPass only, 2 = computeDirection (calcDiff if recalc, then
 // backwardPass) — ddp.cpp:120-125,157-253. The step-wise API runs with iter_ == 0, so problem_->calc is evaluated.
 template <class M>
-__global__ void cta_direction_kernel(const __grid_constant__ CtaCtx c, int what, int recalc) {
+__global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_direction_kernel(const __grid_constant__ CtaCtx c, int what, int recalc) {
   extern __shared__ double cta_smem_raw[];
   const int b = blockIdx.x;
   CtaSmem sm;
@@ -805,7 +815,7 @@ __global__ void cta_direction_kernel(const __grid_constant__ CtaCtx c, int what,
 }
 
 template <class M>
-__global__ void cta_trystep_kernel(const __grid_constant__ CtaCtx c, double alpha) {
+__global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_trystep_kernel(const __grid_constant__ CtaCtx c, double alpha) {
   extern __shared__ double cta_smem_raw[];
   const int b = blockIdx.x;
   CtaSmem sm;
@@ -855,7 +865,7 @@ __global__ void cta_problem_kernel(const __grid_constant__ CtaCtx c, const doubl
 
 // ShootingProblem::rollout (shooting.hxx:198-223) by the block
 template <class M>
-__global__ void cta_rollout_kernel(const __grid_constant__ CtaCtx c, const double* us, double* xs) {
+__global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_rollout_kernel(const __grid_constant__ CtaCtx c, const double* us, double* xs) {
   extern __shared__ double cta_smem_raw[];
   const int b = blockIdx.x, T = c.T, n = c.n, m = c.m;
   CtaSmem sm;

@@ -177,9 +177,19 @@ def oracle_inputs(wl, nsample):
     return params, x0, xs, us
 
 
+def host_threads():
+    """All host threads this process may use (torchrun exports OMP_NUM_THREADS=1: ask the affinity mask instead)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_oracle_rate(wl, nsample, nthreads=0, reps=1):
     """Reference algorithm on the host cores: oracle, -O3 build, OpenMP over problems."""
     import oracle_lib as ol
+
+    nthreads = nthreads or host_threads()
 
     params, x0, xs, us = oracle_inputs(wl, nsample)
     ob = ol.OracleBatch(wl.oracle_kind, "fddp", T, wl.nx, wl.nu, params, x0, fast=True)
@@ -202,10 +212,10 @@ def run_reference(args, wl, rank, world):
     nsample = wl.cpu_sample
     params, x0, xs, us = oracle_inputs(wl, nsample)
     ob = ol.OracleBatch(wl.oracle_kind, "fddp", T, wl.nx, wl.nu, params, x0, fast=True)
-    cores = ob.lib.orc_max_threads()
+    cores = host_threads()
     times = []
     for i in range(args.warmup + args.steps):
-        ob.solve(xs, us, 100, False, wl.reginit, nthreads=0)
+        ob.solve(xs, us, 100, False, wl.reginit, nthreads=cores)
         if i >= args.warmup:
             times.append(ob.seconds)
     tot = sum(times)

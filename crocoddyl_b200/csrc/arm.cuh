@@ -14,8 +14,14 @@
 #include "rigid_body.cuh"
 #include "arm_warp.cuh"
 
+// Block shape of the arm kernels. The backward pass and the rollout are one warp's work, so extra warps only wait at
+// barriers; measured on B200 (B = 8192, T = 100 FDDP): 128 thr x 4 CTAs/SM 1.50 s, 64 x 8 1.17 s, 32 x 16 1.23 s (128
+// registers: spills), 32 x 8 1.13 s <- default.
 #ifndef CGX_ARM_MINBLOCKS
-#define CGX_ARM_MINBLOCKS 4
+#define CGX_ARM_MINBLOCKS 8
+#endif
+#ifndef CGX_ARM_THREADS
+#define CGX_ARM_THREADS 32
 #endif
 
 namespace cgx {
@@ -48,7 +54,7 @@ struct ArmModel {
   static constexpr bool kPerNodeMats = true;
   // the solve kernel is latency-bound (serial recursions over joints and nodes): resident blocks per SM matter more
   // than registers per thread, so the register file is split over CGX_ARM_MINBLOCKS blocks of 128 threads
-  static constexpr int kMinThreads = 128, kMaxThreads = 128, kMinBlocks = CGX_ARM_MINBLOCKS;
+  static constexpr int kMinThreads = CGX_ARM_THREADS, kMaxThreads = CGX_ARM_THREADS, kMinBlocks = CGX_ARM_MINBLOCKS;
   static constexpr int kN = 2 * NV, kM = NV;  // compile-time node sizes for the warp-level backward pass
   const double* params;
 

@@ -61,4 +61,12 @@ def run(sizes=(12, 36, 72), B=4096, T=100, reps=3, peak_tflops=None):
 
 
 if __name__ == "__main__":
-    print(json.dumps(run()))
+    # bench_riccati.py [n ...] [--B batch] [--T horizon]: development knobs for profiling one size on a small batch
+    argv = sys.argv[1:]
+    kw = {}
+    if "--B" in argv:
+        kw["B"] = int(argv[argv.index("--B") + 1])
+    if "--T" in argv:
+        kw["T"] = int(argv[argv.index("--T") + 1])
+    sizes = tuple(int(a) for i, a in enumerate(argv) if a.isdigit() and (i == 0 or argv[i - 1] not in ("--B", "--T")))
+    print(json.dumps(run(sizes or (12, 36, 72), **kw)))

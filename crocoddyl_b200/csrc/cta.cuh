@@ -122,6 +122,78 @@ __device__ void cta_gemm(double* C, int ldc, const double* A, int lda, const dou
 }
 
 // ---------------------------------------------------------------------------------------------
+// The same product on the FP64 tensor cores (DMMA): mma.sync.aligned.m8n8k4.f64, one warp per 8 x 16 output tile
+// (two accumulator fragments sharing the A fragment). Used for the dense n >= 24 products of the Riccati step
+// (Fx^T Vxx Fx at n = 72 is a real 72^3 GEMM); tcgen05 has no FP64 path. Fragment layout of m8n8k4 (PTX ISA):
+//   A (8x4, row): lane l holds A[l/4][l%4]     B (4x8, col): lane l holds B[l%4][l/4]
+//   C/D (8x8)   : lane l holds C[l/4][2(l%4)], C[l/4][2(l%4)+1]
+// Out-of-range operands are read as zero, so any M, N, K works. The k-sum is accumulated in groups of four inside the
+// tensor core instead of one DFMA per k: differences from cta_gemm are at rounding level.
+__device__ __forceinline__ void dmma_8x8x4(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+template <bool TA>
+__device__ void cta_gemm_mma(double* C, int ldc, const double* A, int lda, const double* B, int ldb, int M, int N, int K,
+                             const double* Add, int ldadd, double alpha) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int tm = (M + 7) >> 3, tn = (N + 15) >> 4;
+  const int ar = lane >> 2, ac = lane & 3;  // A fragment: row ar, k-offset ac ; B fragment: k-offset ac, column ar
+  for (int tile = warp; tile < tm * tn; tile += nwarps) {
+    const int i0 = (tile % tm) << 3, j0 = (tile / tm) << 4;
+    const int ia = i0 + ar;
+    const int jb0 = j0 + ar, jb1 = j0 + 8 + ar;
+    const bool oka = ia < M, okb0 = jb0 < N, okb1 = jb1 < N;
+    const bool second = j0 + 8 < N;
+    const double* pa = TA ? (A + (size_t)lda * (oka ? ia : 0)) : (A + (oka ? ia : 0));
+    const double* pb0 = B + (size_t)ldb * (okb0 ? jb0 : 0);
+    const double* pb1 = B + (size_t)ldb * (okb1 ? jb1 : 0);
+    double c00 = 0., c01 = 0., c10 = 0., c11 = 0.;
+    int kk = 0;
+    for (; kk + 4 <= K; kk += 4) {
+      const int k = kk + ac;
+      const double a = oka ? (TA ? pa[k] : pa[(size_t)lda * k]) : 0.;
+      const double b0 = okb0 ? pb0[k] : 0.;
+      dmma_8x8x4(c00, c01, a, b0);
+      if (second) {
+        const double b1 = okb1 ? pb1[k] : 0.;
+        dmma_8x8x4(c10, c11, a, b1);
+      }
+    }
+    if (kk < K) {  // K not a multiple of 4: zero-padded last step
+      const int k = kk + ac;
+      const bool okk = k < K;
+      const double a = (oka && okk) ? (TA ? pa[k] : pa[(size_t)lda * k]) : 0.;
+      const double b0 = (okb0 && okk) ? pb0[k] : 0.;
+      dmma_8x8x4(c00, c01, a, b0);
+      if (second) {
+        const double b1 = (okb1 && okk) ? pb1[k] : 0.;
+        dmma_8x8x4(c10, c11, a, b1);
+      }
+    }
+    const int ci = i0 + ar, cj = j0 + 2 * ac;
+    if (ci < M) {
+      if (cj < N) C[ci + ldc * cj] = (Add ? Add[ci + ldadd * cj] : 0.) + alpha * c00;
+      if (cj + 1 < N) C[ci + ldc * (cj + 1)] = (Add ? Add[ci + ldadd * (cj + 1)] : 0.) + alpha * c01;
+      if (cj + 8 < N) C[ci + ldc * (cj + 8)] = (Add ? Add[ci + ldadd * (cj + 8)] : 0.) + alpha * c10;
+      if (cj + 9 < N) C[ci + ldc * (cj + 9)] = (Add ? Add[ci + ldadd * (cj + 9)] : 0.) + alpha * c11;
+    }
+  }
+}
+// dispatcher: tensor cores for the large products, DFMA register tiles otherwise
+template <bool TA>
+__device__ __forceinline__ void cta_gemm_auto(double* C, int ldc, const double* A, int lda, const double* B, int ldb, int M,
+                                              int N, int K, const double* Add, int ldadd, double alpha) {
+#ifndef CGX_NO_DMMA
+  if (K >= 16 && M >= 8 && N >= 8)
+    cta_gemm_mma<TA>(C, ldc, A, lda, B, ldb, M, N, K, Add, ldadd, alpha);
+  else
+#endif
+    cta_gemm<TA>(C, ldc, A, lda, B, ldb, M, N, K, Add, ldadd, alpha);
+}
+
+// ---------------------------------------------------------------------------------------------
 // ActionModelLQR (reference: include/crocoddyl/core/actions/lqr.hxx:14-70, lqr.hpp:88-95).
 // params = [drift_free, Fx(n*n), Fu(n*m), f0(n), Lxx(n*n), Lxu(n*m), Luu(m*m), lx(n), lu(m)], column-major.
 struct LqrModel {
@@ -268,6 +340,7 @@ struct LqrModel {
   }
 };
 
+// ---------------------------------------------------------------------------------------------
 // ---------------------------------------------------------------------------------------------
 // Shared-memory work area of one block (doubles). Leading dimensions are odd (cta_ld).
 struct CtaSmem {
@@ -416,8 +489,8 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, b
     }
     __syncthreads();
     // A = Fx^T Vxx' ; G = Fu^T Vxx' ; Qx = Lx + Fx^T Vx' ; Qu = Lu + Fu^T Vx'   (ddp.cpp:204,206,211,214)
-    cta_gemm<true>(sm.A, ldn, sm.Fx, ldn, sm.V, ldn, n, n, n, nullptr, 0, 1.);
-    cta_gemm<true>(sm.G, ldm, sm.Fu, ldn, sm.V, ldn, m, n, n, nullptr, 0, 1.);
+    cta_gemm_auto<true>(sm.A, ldn, sm.Fx, ldn, sm.V, ldn, n, n, n, nullptr, 0, 1.);
+    cta_gemm_auto<true>(sm.G, ldm, sm.Fu, ldn, sm.V, ldn, m, n, n, nullptr, 0, 1.);
     for (int j = tid; j < n + m; j += P) {
       double s = 0.;
       if (j < n) {
@@ -431,9 +504,9 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, b
     }
     __syncthreads();
     // Qxx = Lxx + A Fx (into V: Vxx' is dead) ; Qxu = Lxu + A Fu ; Quu = Luu + G Fu (+ ureg)   (ddp.cpp:202-218)
-    cta_gemm<false>(sm.V, ldn, sm.A, ldn, sm.Fx, ldn, n, n, n, nm.Lxx, n, 1.);
-    cta_gemm<false>(sm.Qxu, ldn, sm.A, ldn, sm.Fu, ldn, n, m, n, nm.Lxu, n, 1.);
-    cta_gemm<false>(sm.Quu, ldm, sm.G, ldm, sm.Fu, ldn, m, m, n, nm.Luu, m, 1.);
+    cta_gemm_auto<false>(sm.V, ldn, sm.A, ldn, sm.Fx, ldn, n, n, n, nm.Lxx, n, 1.);
+    cta_gemm_auto<false>(sm.Qxu, ldn, sm.A, ldn, sm.Fu, ldn, n, m, n, nm.Lxu, n, 1.);
+    cta_gemm_auto<false>(sm.Quu, ldm, sm.G, ldm, sm.Fu, ldn, m, m, n, nm.Luu, m, 1.);
     __syncthreads();
     if (has_ureg)
       for (int i = tid; i < m; i += P) sm.Quu[i + ldm * i] += ureg;
@@ -446,10 +519,13 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, b
       for (int i = tid; i < n; i += P) c.Qx[rnode * n + i] = sm.Qx[i];
       for (int i = tid; i < m; i += P) c.Qu[rnode * m + i] = sm.Qu[i];
     }
-    // computeGains (ddp.cpp:298-310): unblocked lower LLT by warp 0, lane i owns row i (rows i, i+32, ...)
+    // computeGains (ddp.cpp:298-310): unblocked lower LLT by warp 0
     if (tid < 32) {
       for (int e = tid; e < m * m; e += 32) sm.Lc[(e % m) + ldm * (e / m)] = sm.Quu[(e % m) + ldm * (e / m)];
       __syncwarp();
+      // lane i owns rows i, i+32, ...: left-looking through shared memory. (A register-resident right-looking variant
+      // with rows/right-hand sides in registers was measured on B200 and is slower: it spills under the 168-register
+      // budget of 384-thread blocks — n = 72: 69.8 vs 64.2 us per sweep.)
       for (int kk = 0; kk < m; ++kk) {
         double p = sm.Lc[kk + ldm * kk];
         for (int j = 0; j < kk; ++j) p -= sm.Lc[kk + ldm * j] * sm.Lc[kk + ldm * j];
@@ -505,7 +581,7 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, b
       }
       sm.Vx[j] = v;
     }
-    cta_gemm<false>(sm.V, ldn, sm.Qxu, ldn, sm.Kg, ldm, n, n, m, sm.V, ldn, -1.);
+    cta_gemm_auto<false>(sm.V, ldn, sm.Qxu, ldn, sm.Kg, ldm, n, n, m, sm.V, ldn, -1.);
     if (tid == 0) {  // ddp.cpp:132-155 / fddp.cpp:137-140
       double a = 0., q = 0., st = 0.;
       for (int i = 0; i < m; ++i) {

@@ -15,7 +15,7 @@ LIB = os.path.join(LIBDIR, "libcrocoddyl_b200.so")
 # per-source extra flags. tpp_backend.cu: the thread-per-problem solve kernel must stay <= 128 registers so
 # that 65,536 problems are resident in ONE wave (8 blocks x 64 threads per SM; measured: 144 registers already falls back to two waves).
 EXTRA = {"tpp_backend.cu": ["-maxrregcount=128"]}
-SOURCES = ["capi.cu", "tpp_backend.cu", "cta_backend.cu"]
+SOURCES = ["cta_arm7.cu", "cta_arm4.cu", "cta_arm2.cu", "cta_backend.cu", "tpp_backend.cu", "capi.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-Xcompiler", "-fvisibility=hidden"]
 

@@ -52,6 +52,8 @@ __global__ void arm_quasi_static_kernel(const double* params, long nparams, int 
 template <int NV>
 struct ArmModel {
   static constexpr bool kPerNodeMats = true;
+  // solve() as lockstep phase launches instead of the fused per-problem loop (cta.cuh, measured 2x faster: i-cache)
+  static constexpr bool kPhaseSplit = true;
   // the solve kernel is latency-bound (serial recursions over joints and nodes): resident blocks per SM matter more
   // than registers per thread, so the register file is split over CGX_ARM_MINBLOCKS blocks of 128 threads
   static constexpr int kMinThreads = CGX_ARM_THREADS, kMaxThreads = CGX_ARM_THREADS, kMinBlocks = CGX_ARM_MINBLOCKS;

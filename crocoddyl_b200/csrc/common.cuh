@@ -23,7 +23,9 @@ enum {
 // per-problem int slots, iscal[slot * Bp + b]
 enum {
   I_ITER = 0, I_FEAS, I_WASFEAS, I_CONVERGED, I_CUR, I_NREC, I_BSTATUS, I_FSTATUS, I_NBWD, I_NFWD, I_FSBUF,
-  I_LOOP /* resumable solve loop: bit 0 recalcDiff, bit 1 gaps must be recomputed */, I_FINISHED, I_NSLOTS
+  I_LOOP /* resumable solve loop: bit 0 recalcDiff, bit 1 gaps must be recomputed */, I_FINISHED,
+  I_PHASE /* phase-split solve (cta.cuh): 0 computeDirection pending, 1 line search pending, 2 solve() returned */,
+  I_ALPHA /* phase-split solve: index of the next step length to try */, I_RETRIES, I_NSLOTS
 };
 
 // raiseIfNaN (reference: src/core/solver-base.cpp:175-181)

@@ -198,6 +198,7 @@ __device__ __forceinline__ void cta_gemm_auto(double* C, int ldc, const double* 
 // params = [drift_free, Fx(n*n), Fu(n*m), f0(n), Lxx(n*n), Lxu(n*m), Luu(m*m), lx(n), lu(m)], column-major.
 struct LqrModel {
   static constexpr bool kPerNodeMats = false;
+  static constexpr bool kPhaseSplit = false;  // the fused solve kernel is small for LQR
   static constexpr int kMinThreads = 64, kMaxThreads = 384, kMinBlocks = 1;
   static constexpr int kN = 0, kM = 0;  // run-time sizes
   const double *Fx, *Fu, *f0, *Lxx, *Lxu, *Luu, *lx, *lu;
@@ -855,6 +856,176 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_solve_kerne
 }
 
 // ---------------------------------------------------------------------------------------------
+// Phase-split solve: the same loop as cta_solve_kernel cut at its two heavy calls, one launch per phase for the whole
+// batch, driven by the host (CtaBackend::solve_phases) until every problem has returned. Why: the fused arm kernel is
+// ~50k SASS instructions; with every warp of an SM at a different place of the loop the instruction cache thrashes
+// (ncu: stall_no_instruction = half of all stall cycles) and the fused kernel measured 2.3x slower than the sum of
+// its phases run in lockstep. The loop variables live in the per-problem slots between launches; the arithmetic is
+// the same device functions in the same order, so results are identical to the fused kernel.
+//   cta_phase_direction_kernel : problems in phase 0 — computeDirection incl. ONE regularisation retry per launch
+//   cta_phase_forward_kernel   : problems in phase 1 — ONE trial of the line search + the end-of-iteration bookkeeping
+static __global__ void cta_phase_init_kernel(const __grid_constant__ CtaCtx c, int maxiter, int is_feasible0, double reginit) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= c.B) return;
+  const double xreg = isnan(reginit) ? c.o.regmin : reginit;
+  CTA_S(S_XREG) = xreg;
+  CTA_S(S_UREG) = xreg;
+  CTA_S(S_DG) = 0.;
+  CTA_S(S_DQ) = 0.;
+  CTA_I(I_FEAS) = is_feasible0 != 0;
+  CTA_I(I_WASFEAS) = 0;
+  CTA_I(I_ITER) = 0;
+  CTA_I(I_NREC) = 0;
+  CTA_I(I_NBWD) = 0;
+  CTA_I(I_NFWD) = 0;
+  CTA_I(I_CONVERGED) = 0;
+  CTA_I(I_LOOP) = 1;  // recalcDiff
+  CTA_I(I_ALPHA) = 0;
+  CTA_I(I_RETRIES) = 0;
+  CTA_I(I_PHASE) = maxiter > 0 ? 0 : 2;
+}
+
+template <class M>
+__global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_phase_direction_kernel(const __grid_constant__ CtaCtx c, int* active) {
+  extern __shared__ double cta_smem_raw[];
+  const int b = blockIdx.x;
+  const int phase = CTA_I(I_PHASE);
+  if (phase != 2 && threadIdx.x == 0) atomicAdd(active, 1);  // problems whose solve() has not returned yet
+  if (phase != 0) return;
+  CtaSmem sm;
+  sm.carve(cta_smem_raw, c.n, c.m);
+  M mod;
+  mod.load(c, b);
+  const int cur = CTA_I(I_CUR), iter = CTA_I(I_ITER);
+  const bool feas = CTA_I(I_FEAS) != 0, wasfeas = CTA_I(I_WASFEAS) != 0, recalc = (CTA_I(I_LOOP) & 1) != 0;
+  double xreg = CTA_S(S_XREG), ureg = CTA_S(S_UREG);
+  double dg = CTA_S(S_DG), dq = CTA_S(S_DQ), stop = CTA_S(S_STOP);  // kept when the backward pass fails
+  __syncthreads();
+  double cost = 0.;
+  if (recalc) cost = cta_calcdiff(c, mod, sm, b, cur, iter == 0, feas, wasfeas);
+  const int st = cta_backward(c, mod, sm, b, feas, xreg, ureg, dg, dq, stop);
+  if (threadIdx.x != 0) return;
+  if (recalc) CTA_S(S_COST) = cost;
+  ++CTA_I(I_NBWD);
+  CTA_I(I_LOOP) = 0;
+  CTA_S(S_DG) = dg;
+  CTA_S(S_DQ) = dq;
+  CTA_S(S_STOP) = stop;
+  if (st != 0) {  // ddp.cpp:55-68: increase the regularisation and try again (next launch)
+    reg_increase(c.o, xreg, ureg);
+    CTA_S(S_XREG) = xreg;
+    CTA_S(S_UREG) = ureg;
+    ++CTA_I(I_RETRIES);
+    if (xreg == c.o.regmax) CTA_I(I_PHASE) = 2;
+    return;
+  }
+  if (!c.fddp) {
+    CTA_S(S_D0) = dg;
+    CTA_S(S_D1) = dq;
+  }
+  CTA_I(I_ALPHA) = 0;
+  CTA_I(I_PHASE) = 1;
+}
+
+template <class M>
+__global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_phase_forward_kernel(const __grid_constant__ CtaCtx c, int maxiter) {
+  extern __shared__ double cta_smem_raw[];
+  const int b = blockIdx.x;
+  if (CTA_I(I_PHASE) != 1) return;
+  CtaSmem sm;
+  sm.carve(cta_smem_raw, c.n, c.m);
+  M mod;
+  mod.load(c, b);
+  const bool fddp = c.fddp != 0;
+  int cur = CTA_I(I_CUR);
+  bool feas = CTA_I(I_FEAS) != 0, wasfeas = CTA_I(I_WASFEAS) != 0;
+  const int a = CTA_I(I_ALPHA);
+  const double steplength = c.o.alphas[a];
+  double cost = CTA_S(S_COST), cost_try = CTA_S(S_COST_TRY), d0 = CTA_S(S_D0), d1 = CTA_S(S_D1);
+  double dV = CTA_S(S_DV), dVexp = CTA_S(S_DVEXP);
+  const double dg = CTA_S(S_DG), dq = CTA_S(S_DQ), stop = CTA_S(S_STOP);
+  double xreg = CTA_S(S_XREG), ureg = CTA_S(S_UREG);
+  __syncthreads();
+  double dv = 0.;
+  const int st = cta_forward(c, mod, sm, b, cur, steplength, feas, cost_try, dv);
+  if (threadIdx.x != 0) return;
+  ++CTA_I(I_NFWD);
+  int accepted = -1;
+  bool recalc = false;
+  if (!st) {
+    dV = cost - cost_try;
+    if (fddp) {
+      d0 = dg + dv;
+      d1 = dq - 2 * dv;
+    }
+    dVexp = steplength * (d0 + 0.5 * steplength * d1);
+    if (cta_accept(c.o, fddp, feas, d0, dV, dVexp)) {
+      wasfeas = feas;
+      feas = fddp ? (wasfeas || (steplength == 1.)) : true;
+      cost = cost_try;
+      cur ^= 1;
+      recalc = true;
+      accepted = a;
+    }
+  }
+  CTA_S(S_STEP) = steplength;
+  CTA_S(S_COST_TRY) = cost_try;
+  CTA_S(S_DV) = dV;
+  CTA_S(S_DVEXP) = dVexp;
+  CTA_S(S_D0) = d0;
+  CTA_S(S_D1) = d1;
+  if (accepted < 0 && a + 1 < c.o.nalphas) {  // next step length at the next launch
+    CTA_I(I_ALPHA) = a + 1;
+    return;
+  }
+  CTA_S(S_COST) = cost;
+  CTA_I(I_CUR) = cur;
+  CTA_I(I_FEAS) = feas;
+  CTA_I(I_WASFEAS) = wasfeas;
+  CTA_I(I_LOOP) = recalc ? 1 : 0;
+  // end of the iteration: ddp.cpp:93-116 / fddp.cpp:80-103
+  if (steplength > c.o.th_stepdec) reg_decrease(c.o, xreg, ureg);
+  bool done = false;
+  if (steplength <= c.o.th_stepinc) {
+    reg_increase(c.o, xreg, ureg);
+    if (xreg == c.o.regmax) done = true;
+  }
+  CTA_S(S_XREG) = xreg;
+  CTA_S(S_UREG) = ureg;
+  int iter = CTA_I(I_ITER);
+  if (!done) {
+    const int nrec = CTA_I(I_NREC);
+    if (c.trace && nrec < c.trace_cap) {
+      double* tr = c.trace + ((size_t)b * c.trace_cap + nrec) * NTRACE;
+      tr[0] = iter;
+      tr[1] = cost;
+      tr[2] = stop;
+      tr[3] = d0;
+      tr[4] = d1;
+      tr[5] = xreg;
+      tr[6] = ureg;
+      tr[7] = steplength;
+      tr[8] = feas ? 1. : 0.;
+      tr[9] = dV;
+      tr[10] = dVexp;
+      tr[11] = accepted;
+      tr[12] = CTA_I(I_RETRIES);
+    }
+    CTA_I(I_NREC) = nrec + 1;
+    if (wasfeas && stop < c.o.th_stop) {
+      CTA_I(I_CONVERGED) = 1;
+      done = true;
+    } else {
+      ++iter;
+      if (iter >= maxiter) done = true;
+    }
+  }
+  CTA_I(I_ITER) = iter;
+  CTA_I(I_RETRIES) = 0;
+  CTA_I(I_PHASE) = done ? 2 : 0;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Step-wise kernels. what: 0 = calcDiff only, 1 = backwardPass only, 2 = computeDirection (calcDiff if recalc, then
 // backwardPass) — ddp.cpp:120-125,157-253. The step-wise API runs with iter_ == 0, so problem_->calc is evaluated.
 template <class M>
@@ -967,7 +1138,7 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_rollout_ker
 }
 
 // per-problem bookkeeping of setCandidate + scalar export
-__global__ void cta_reset_kernel(CtaCtx c, int is_feasible) {
+static __global__ void cta_reset_kernel(CtaCtx c, int is_feasible) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= c.B) return;
   CTA_I(I_ITER) = 0;
@@ -982,7 +1153,7 @@ __global__ void cta_reset_kernel(CtaCtx c, int is_feasible) {
   CTA_I(I_NFWD) = 0;
   CTA_S(S_DVGAP) = 0.;
 }
-__global__ void cta_scalars_kernel(CtaCtx c, double* out) {
+static __global__ void cta_scalars_kernel(CtaCtx c, double* out) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= c.B) return;
   double* o = out + (size_t)b * 17;
@@ -1004,14 +1175,14 @@ __global__ void cta_scalars_kernel(CtaCtx c, double* out) {
   o[15] = CTA_I(I_NBWD);
   o[16] = CTA_I(I_NFWD);
 }
-__global__ void cta_setreg_kernel(CtaCtx c, double xreg, double ureg, int set_x, int set_u) {
+static __global__ void cta_setreg_kernel(CtaCtx c, double xreg, double ureg, int set_x, int set_u) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= c.B) return;
   if (set_x) CTA_S(S_XREG) = xreg;
   if (set_u) CTA_S(S_UREG) = ureg;
 }
 // out[b][...] = field of problems b0.. : per-problem contiguous copy, selecting the candidate/trial buffer
-__global__ void cta_copy_sel_kernel(double* out, const double* a0, const double* a1, const int* sel, int flip,
+static __global__ void cta_copy_sel_kernel(double* out, const double* a0, const double* a1, const int* sel, int flip,
                                     size_t per_problem, int b0, int to_field) {
   const int b = b0 + blockIdx.y;
   const double* src = (sel && ((sel[b] ^ flip) & 1)) ? a1 : a0;

@@ -1,294 +1,19 @@
-// crocoddyl_b200 — host driver of the CTA-per-problem kernels (cta.cuh). Model families: LQR, revolute-chain arm.
-#include <cstring>
-#include "backend.hpp"
-#include "cta.cuh"
-#include "arm.cuh"
+// crocoddyl_b200 — CTA-per-problem backend: LQR instantiation and the model factory.
+#include "cta_backend.cuh"
 
 namespace cgx {
 
-namespace {
-
-template <class M>
-struct CtaBackend : Backend {
-  CtaCtx c;
-  std::vector<void*> allocs;
-  bool solver_allocated = false, data_allocated = false;
-  int threads = 128;
-  size_t smem = 0;
-
-  explicit CtaBackend(const ProblemDesc* p_, int sk) {
-    p = p_;
-    solver_kind = sk;
-    std::memset(&c, 0, sizeof(c));
-    c.B = p->B;
-    c.Bp = p->B;
-    c.T = p->T;
-    c.n = p->nx;
-    c.m = p->nu;
-    c.fddp = sk == 1;
-    c.model_kind = p->kind;
-    c.params = p->d_params;
-    c.nparams = p->nparams;
-    c.per_problem = p->per_problem_params;
-    c.x0 = p->d_x0;
-    CGX_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 4; ++i) CGX_CUDA(cudaEventCreate(&ev[i]));
-    const int tn = (c.n + 3) / 4;
-    threads = ((tn * tn + 31) / 32) * 32;
-    if (threads < M::kMinThreads) threads = M::kMinThreads;
-    if (threads > M::kMaxThreads) threads = M::kMaxThreads;
-    smem = cta_smem_bytes(c.n, c.m);
-    int dev = 0, maxsm = 0;
-    CGX_CUDA(cudaGetDevice(&dev));
-    CGX_CUDA(cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-    if (smem > (size_t)maxsm)
-      throw Unsupported("problem too large for one thread block's shared memory (nx = " + std::to_string(c.n) + ")");
-    CGX_CUDA(cudaFuncSetAttribute(cta_solve_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CGX_CUDA(cudaFuncSetAttribute(cta_direction_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CGX_CUDA(cudaFuncSetAttribute(cta_trystep_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CGX_CUDA(cudaFuncSetAttribute(cta_rollout_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  }
-  ~CtaBackend() override {
-    for (void* q : allocs) cudaFree(q);
-    for (int i = 0; i < 4; ++i)
-      if (ev[i]) cudaEventDestroy(ev[i]);
-    if (stream) cudaStreamDestroy(stream);
-  }
-  double* alloc(size_t n) {
-    double* q = dalloc<double>(n);
-    CGX_CUDA(cudaMemsetAsync(q, 0, (n ? n : 1) * sizeof(double), stream));
-    allocs.push_back(q);
-    return q;
-  }
-  void release(double*& q) {
-    if (!q) return;
-    for (size_t i = 0; i < allocs.size(); ++i)
-      if (allocs[i] == q) {
-        allocs.erase(allocs.begin() + i);
-        break;
-      }
-    cudaFree(q);
-    q = nullptr;
-  }
-  int sblocks() const { return (c.B + 127) / 128; }
-  void x0_changed() override {}
-
-  void ensure_data() {
-    if (data_allocated) return;
-    const size_t B = c.B, T = c.T, n = c.n, m = c.m;
-    c.d_cost = alloc(B * (T + 1));
-    c.d_xnext = alloc(B * (T + 1) * n);
-    c.d_Lx = alloc(B * (T + 1) * n);
-    c.d_Lu = alloc(B * (T + 1) * (m ? m : 1));
-    if (M::kPerNodeMats) {
-      c.d_Fx = alloc(B * (T + 1) * n * n);
-      c.d_Fu = alloc(B * (T + 1) * n * m);
-      c.d_Lxx = alloc(B * (T + 1) * n * n);
-      c.d_Lxu = alloc(n * m);  // identically zero for the arm's cost set: one shared block
-      c.d_Luu = alloc(B * (T + 1) * m * m);
-    }
-    data_allocated = true;
-  }
-
-  void configure() override {
-    c.o = o;
-    const size_t B = c.B, T = c.T, n = c.n, m = c.m;
-    ensure_data();
-    if (!solver_allocated) {
-      for (int i = 0; i < 2; ++i) {
-        c.xs[i] = alloc(B * (T + 1) * n);
-        c.us[i] = alloc(B * T * m);
-      }
-      c.fs = alloc(B * (T + 1) * n);
-      c.K = alloc(B * T * m * n);
-      c.k = alloc(B * T * m);
-      c.Vx = alloc(B * (T + 1) * n);
-      c.Vxx = alloc(B * (T + 1) * n * n);
-      c.w = alloc(B * (T + 1) * n);
-      c.scal = alloc((size_t)S_NSLOTS * c.Bp);
-      int* is = dalloc<int>((size_t)I_NSLOTS * c.Bp);
-      allocs.push_back(is);
-      c.iscal = is;
-      CGX_CUDA(cudaMemsetAsync(is, 0, (size_t)I_NSLOTS * c.Bp * sizeof(int), stream));
-      std::vector<double> h((size_t)S_NSLOTS * c.Bp, 0.);
-      for (size_t b = 0; b < (size_t)c.Bp; ++b) {
-        h[(size_t)S_XREG * c.Bp + b] = NAN;  // solver-base.cpp:14-25
-        h[(size_t)S_UREG * c.Bp + b] = NAN;
-        h[(size_t)S_STEP * c.Bp + b] = 1.;
-      }
-      CGX_CUDA(cudaMemcpyAsync(c.scal, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice, stream));
-      CGX_CUDA(cudaStreamSynchronize(stream));
-      solver_allocated = true;
-    }
-    if (full && !c.Qxx) {
-      c.Qxx = alloc(B * T * n * n);
-      c.Qxu = alloc(B * T * n * m);
-      c.Quu = alloc(B * T * m * m);
-      c.Qx = alloc(B * T * n);
-      c.Qu = alloc(B * T * m);
-    }
-    c.full = full;
-    if (trace_on && (!c.trace || c.trace_cap != trace_cap)) {
-      release(c.trace);
-      c.trace = alloc(B * (size_t)trace_cap * NTRACE);
-      c.trace_cap = trace_cap;
-    }
-    if (!trace_on) {
-      release(c.trace);
-      c.trace_cap = 0;
-    }
-  }
-
-  void set_candidate(const double* d_xs, const double* d_us, int is_feasible) override {
-    const size_t B = c.B, T = c.T, n = c.n, m = c.m;
-    cta_reset_kernel<<<sblocks(), 128, 0, stream>>>(c, is_feasible);
-    ++last_launches;
-    if (d_xs)
-      CGX_CUDA(cudaMemcpyAsync(c.xs[0], d_xs, B * (T + 1) * n * sizeof(double), cudaMemcpyDeviceToDevice, stream));
-    else
-      CGX_CUDA(cudaMemsetAsync(c.xs[0], 0, B * (T + 1) * n * sizeof(double), stream));
-    if (d_us)
-      CGX_CUDA(cudaMemcpyAsync(c.us[0], d_us, B * T * m * sizeof(double), cudaMemcpyDeviceToDevice, stream));
-    else
-      CGX_CUDA(cudaMemsetAsync(c.us[0], 0, B * T * m * sizeof(double), stream));
-  }
-
-  void solve(int maxiter, int is_feasible, double reginit) override {
-    c.o = o;
-    CGX_CUDA(cudaEventRecord(ev[1], stream));
-    cta_solve_kernel<M><<<c.B, threads, smem, stream>>>(c, maxiter, is_feasible, reginit);
-    CGX_CUDA(cudaEventRecord(ev[2], stream));
-    ++last_launches;
-    CGX_CUDA(cudaGetLastError());
-  }
-  void compute_direction(int recalc) override {
-    c.o = o;
-    CGX_CUDA(cudaEventRecord(ev[1], stream));
-    cta_direction_kernel<M><<<c.B, threads, smem, stream>>>(c, 2, recalc);
-    CGX_CUDA(cudaEventRecord(ev[2], stream));
-    ++last_launches;
-    CGX_CUDA(cudaGetLastError());
-  }
-  void try_step(double alpha) override {
-    c.o = o;
-    CGX_CUDA(cudaEventRecord(ev[1], stream));
-    cta_trystep_kernel<M><<<c.B, threads, smem, stream>>>(c, alpha);
-    CGX_CUDA(cudaEventRecord(ev[2], stream));
-    ++last_launches;
-    CGX_CUDA(cudaGetLastError());
-  }
-
-  struct Fld {
-    double* a;
-    double* b;
-    int flip, size, nt;
-    bool dbl;
-  };
-  Fld fld(const std::string& nme) {
-    const int T = c.T, n = c.n, m = c.m;
-    if (nme == "xs") return {c.xs[0], c.xs[1], 0, n, T + 1, true};
-    if (nme == "xs_try") return {c.xs[0], c.xs[1], 1, n, T + 1, true};
-    if (nme == "us") return {c.us[0], c.us[1], 0, m, T, true};
-    if (nme == "us_try") return {c.us[0], c.us[1], 1, m, T, true};
-    if (nme == "fs") return {c.fs, c.fs, 0, n, T + 1, false};
-    if (nme == "K") return {c.K, c.K, 0, m * n, T, false};
-    if (nme == "k") return {c.k, c.k, 0, m, T, false};
-    if (nme == "Vx") return {c.Vx, c.Vx, 0, n, T + 1, false};
-    if (nme == "Vxx") return {c.Vxx, c.Vxx, 0, n * n, T + 1, false};
-    if (nme == "Qxx" || nme == "Qxu" || nme == "Quu" || nme == "Qx" || nme == "Qu") {
-      if (!c.full || !c.Qxx)
-        throw Unsupported("field " + nme + " is not kept with cgx_solver_set_storage(full = 0)");
-      if (nme == "Qxx") return {c.Qxx, c.Qxx, 0, n * n, T, false};
-      if (nme == "Qxu") return {c.Qxu, c.Qxu, 0, n * m, T, false};
-      if (nme == "Quu") return {c.Quu, c.Quu, 0, m * m, T, false};
-      if (nme == "Qx") return {c.Qx, c.Qx, 0, n, T, false};
-      return {c.Qu, c.Qu, 0, m, T, false};
-    }
-    throw NotFound("unknown field " + nme);
-  }
-  FieldInfo field_info(const std::string& name) override {
-    Fld f = fld(name);
-    return {f.size, f.nt};
-  }
-  void copy_sel(double* d_user, const Fld& f, int b0, int nb, int to_field) {
-    const size_t per = (size_t)f.size * f.nt;
-    if (per == 0) return;
-    int gx = (int)((per + 255) / 256);
-    if (gx > 64) gx = 64;
-    cta_copy_sel_kernel<<<dim3(gx, nb), 256, 0, stream>>>(d_user, f.a, f.b, f.dbl ? c.iscal + (size_t)I_CUR * c.Bp : nullptr,
-                                                          f.flip, per, b0, to_field);
-    ++last_launches;
-  }
-  void export_field(const std::string& name, int b0, int nb, double* d_out) override { copy_sel(d_out, fld(name), b0, nb, 0); }
-  void import_field(const std::string& name, const double* d_in) override {
-    if (name != "xs" && name != "us") throw Unsupported("only xs and us can be set");
-    copy_sel(const_cast<double*>(d_in), fld(name), 0, c.B, 1);
-  }
-  void export_scalars(double* d_out) override {
-    cta_scalars_kernel<<<sblocks(), 128, 0, stream>>>(c, d_out);
-    ++last_launches;
-  }
-  void export_status(int which, int* d_out) override {
-    CGX_CUDA(cudaMemcpyAsync(d_out, c.iscal + (size_t)(which ? I_FSTATUS : I_BSTATUS) * c.Bp, c.B * sizeof(int),
-                             cudaMemcpyDeviceToDevice, stream));
-  }
-  void set_reg(double xreg, double ureg, bool set_x, bool set_u) override {
-    cta_setreg_kernel<<<sblocks(), 128, 0, stream>>>(c, xreg, ureg, set_x, set_u);
-  }
-  void export_trace(int b, double* d_out) override {
-    if (!c.trace) throw InvalidArg("trace recording is not enabled (cgx_solver_enable_trace)");
-    CGX_CUDA(cudaMemcpyAsync(d_out, c.trace + (size_t)b * c.trace_cap * NTRACE, (size_t)c.trace_cap * NTRACE * sizeof(double),
-                             cudaMemcpyDeviceToDevice, stream));
-  }
-
-  // ---- problem-level API ----
-  void problem_calc(const double* d_xs, const double* d_us, int diff, double* d_costs) override {
-    ensure_data();
-    cta_problem_kernel<M><<<c.B, 128, 0, stream>>>(c, d_xs, d_us, diff, d_costs);
-    ++last_launches;
-  }
-  void problem_rollout(const double* d_us, double* d_xs) override {
-    ensure_data();
-    cta_rollout_kernel<M><<<c.B, threads, smem, stream>>>(c, d_us, d_xs);
-    ++last_launches;
-  }
-  void problem_quasi_static(const double* d_x, double* d_u) override { M::quasi_static(*this, c, d_x, d_u, stream); }
-  FieldInfo data_info(const std::string& name) override {
-    const int T = c.T, n = c.n, m = c.m;
-    if (name == "cost") return {1, T + 1};
-    if (name == "xnext") return {n, T + 1};
-    if (name == "Fx") return {n * n, T + 1};
-    if (name == "Fu") return {n * m, T + 1};
-    if (name == "Lx") return {n, T + 1};
-    if (name == "Lu") return {m, T + 1};
-    if (name == "Lxx") return {n * n, T + 1};
-    if (name == "Lxu") return {n * m, T + 1};
-    if (name == "Luu") return {m * m, T + 1};
-    throw NotFound("unknown data field " + name);
-  }
-  void export_data(const std::string& name, int b, int t, double* d_out) override {
-    ensure_data();
-    FieldInfo fi = data_info(name);
-    const size_t node = (size_t)b * (c.T + 1) + t;
-    const double* src = nullptr;
-    if (name == "cost") src = c.d_cost + node;
-    else if (name == "xnext") src = c.d_xnext + node * c.n;
-    else if (name == "Lx") src = c.d_Lx + node * c.n;
-    else if (name == "Lu") src = c.d_Lu + node * c.m;
-    else src = M::node_matrix(c, p, name, b, t);
-    CGX_CUDA(cudaMemcpyAsync(d_out, src, fi.size * sizeof(double), cudaMemcpyDeviceToDevice, stream));
-  }
-};
-
-}  // namespace
+Backend* make_cta_arm2_backend(const ProblemDesc* p, int solver_kind);
+Backend* make_cta_arm4_backend(const ProblemDesc* p, int solver_kind);
+Backend* make_cta_arm7_backend(const ProblemDesc* p, int solver_kind);
 
 Backend* make_cta_backend(const ProblemDesc* p, int solver_kind) {
   if (p->kind == 0) return new CtaBackend<LqrModel>(p, solver_kind);
   if (p->kind == 2) {
     switch (p->nu) {
-      case 2: return new CtaBackend<ArmModel<2> >(p, solver_kind);
-      case 4: return new CtaBackend<ArmModel<4> >(p, solver_kind);
-      case 7: return new CtaBackend<ArmModel<7> >(p, solver_kind);
+      case 2: return make_cta_arm2_backend(p, solver_kind);
+      case 4: return make_cta_arm4_backend(p, solver_kind);
+      case 7: return make_cta_arm7_backend(p, solver_kind);
       default:
         throw Unsupported("arm model: kernels are instantiated for nv = 2, 4 and 7 joints (got nv = " +
                           std::to_string(p->nu) + ")");

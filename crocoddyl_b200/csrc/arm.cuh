@@ -20,6 +20,12 @@
 #ifndef CGX_ARM_MINBLOCKS
 #define CGX_ARM_MINBLOCKS 8
 #endif
+#ifndef CGX_ARM_DIR_MINBLOCKS
+#define CGX_ARM_DIR_MINBLOCKS 8
+#endif
+#ifndef CGX_ARM_FWD_MINBLOCKS
+#define CGX_ARM_FWD_MINBLOCKS 8
+#endif
 #ifndef CGX_ARM_THREADS
 #define CGX_ARM_THREADS 32
 #endif
@@ -54,9 +60,13 @@ struct ArmModel {
   static constexpr bool kPerNodeMats = true;
   // solve() as lockstep phase launches instead of the fused per-problem loop (cta.cuh, measured 2x faster: i-cache)
   static constexpr bool kPhaseSplit = true;
+  // calc/calcDiff of the phase-split solve run as ONE launch over all (problem, node) pairs of the batch
+  static constexpr bool kNodeKernel = true;
   // the solve kernel is latency-bound (serial recursions over joints and nodes): resident blocks per SM matter more
   // than registers per thread, so the register file is split over CGX_ARM_MINBLOCKS blocks of 128 threads
   static constexpr int kMinThreads = CGX_ARM_THREADS, kMaxThreads = CGX_ARM_THREADS, kMinBlocks = CGX_ARM_MINBLOCKS;
+  // resident blocks per SM of the phase-split kernels (backward pass only / one line-search trial)
+  static constexpr int kDirMinBlocks = CGX_ARM_DIR_MINBLOCKS, kFwdMinBlocks = CGX_ARM_FWD_MINBLOCKS;
   static constexpr int kN = 2 * NV, kM = NV;  // compile-time node sizes for the warp-level backward pass
   const double* params;
 
@@ -81,37 +91,40 @@ struct ArmModel {
     return NodeMats{c.d_Fx + node * n * n, c.d_Fu + node * n * m, c.d_Lxx + node * n * n, nullptr,
                     c.d_Luu + node * m * m, false};
   }
-  __device__ void calc_all(const CtaCtx& c, int b, const double* xs, const double* us) const {
+  // one node by the calling thread (xs, us: this problem's trajectories)
+  __device__ void calc_node(const CtaCtx& c, int b, int t, const double* xs, const double* us) const {
     const int T = c.T;
-    for (int t = threadIdx.x; t <= T; t += blockDim.x) {
-      const size_t node = (size_t)b * (T + 1) + t;
-      double x[2 * NV], u[NV], xn[2 * NV];
+    const size_t node = (size_t)b * (T + 1) + t;
+    double x[2 * NV], u[NV], xn[2 * NV];
 #pragma unroll
-      for (int i = 0; i < 2 * NV; ++i) x[i] = xs[(size_t)t * 2 * NV + i];
-      if (t < T) {
+    for (int i = 0; i < 2 * NV; ++i) x[i] = xs[(size_t)t * 2 * NV + i];
+    if (t < T) {
 #pragma unroll
-        for (int i = 0; i < NV; ++i) u[i] = us[(size_t)t * NV + i];
-      }
-      c.d_cost[node] = arm_calc_node_dev<NV>(params, t == T, x, t < T ? u : nullptr, xn);
-#pragma unroll
-      for (int i = 0; i < 2 * NV; ++i) c.d_xnext[node * 2 * NV + i] = xn[i];
+      for (int i = 0; i < NV; ++i) u[i] = us[(size_t)t * NV + i];
     }
+    c.d_cost[node] = arm_calc_node_dev<NV>(params, t == T, x, t < T ? u : nullptr, xn);
+#pragma unroll
+    for (int i = 0; i < 2 * NV; ++i) c.d_xnext[node * 2 * NV + i] = xn[i];
   }
-  __device__ void calcdiff_all(const CtaCtx& c, int b, const double* xs, const double* us) const {
+  __device__ void calcdiff_node(const CtaCtx& c, int b, int t, const double* xs, const double* us) const {
     const int T = c.T;
     constexpr size_t n = 2 * NV, m = NV;
-    for (int t = threadIdx.x; t <= T; t += blockDim.x) {
-      const size_t node = (size_t)b * (T + 1) + t;
-      double x[2 * NV], u[NV];
+    const size_t node = (size_t)b * (T + 1) + t;
+    double x[2 * NV], u[NV];
 #pragma unroll
-      for (int i = 0; i < 2 * NV; ++i) x[i] = xs[(size_t)t * 2 * NV + i];
-      if (t < T) {
+    for (int i = 0; i < 2 * NV; ++i) x[i] = xs[(size_t)t * 2 * NV + i];
+    if (t < T) {
 #pragma unroll
-        for (int i = 0; i < NV; ++i) u[i] = us[(size_t)t * NV + i];
-      }
-      arm_calcdiff_node_dev<NV>(params, t == T, x, t < T ? u : nullptr, c.d_Fx + node * n * n, c.d_Fu + node * n * m,
-                                c.d_Lx + node * n, c.d_Lu + node * m, c.d_Lxx + node * n * n, c.d_Luu + node * m * m);
+      for (int i = 0; i < NV; ++i) u[i] = us[(size_t)t * NV + i];
     }
+    arm_calcdiff_node_dev<NV>(params, t == T, x, t < T ? u : nullptr, c.d_Fx + node * n * n, c.d_Fu + node * n * m,
+                              c.d_Lx + node * n, c.d_Lu + node * m, c.d_Lxx + node * n * n, c.d_Luu + node * m * m);
+  }
+  __device__ void calc_all(const CtaCtx& c, int b, const double* xs, const double* us) const {
+    for (int t = threadIdx.x; t <= c.T; t += blockDim.x) calc_node(c, b, t, xs, us);
+  }
+  __device__ void calcdiff_all(const CtaCtx& c, int b, const double* xs, const double* us) const {
+    for (int t = threadIdx.x; t <= c.T; t += blockDim.x) calcdiff_node(c, b, t, xs, us);
   }
   // calc of one node for the rollout: x, u (null at the terminal node) and xnext in shared memory; warp 0 evaluates
   // it cooperatively (arm_warp.cuh), the other warps of the block wait

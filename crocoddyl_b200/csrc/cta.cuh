@@ -199,7 +199,8 @@ __device__ __forceinline__ void cta_gemm_auto(double* C, int ldc, const double* 
 struct LqrModel {
   static constexpr bool kPerNodeMats = false;
   static constexpr bool kPhaseSplit = false;  // the fused solve kernel is small for LQR
-  static constexpr int kMinThreads = 64, kMaxThreads = 384, kMinBlocks = 1;
+  static constexpr bool kNodeKernel = false;
+  static constexpr int kMinThreads = 64, kMaxThreads = 384, kMinBlocks = 1, kDirMinBlocks = 1, kFwdMinBlocks = 1;
   static constexpr int kN = 0, kM = 0;  // run-time sizes
   const double *Fx, *Fu, *f0, *Lxx, *Lxu, *Luu, *lx, *lu;
   bool drift_free;
@@ -382,9 +383,13 @@ struct CtaSmem {
     flag = reinterpret_cast<int*>(p);
   }
 };
-inline size_t cta_smem_bytes(int n, int m) {
+// the block-wide plan alone (CtaSmem::carve): what the rollout / line-search kernels touch
+inline size_t cta_blockwide_smem_bytes(int n, int m) {
   const size_t ldn = n | 1, ldm = (m | 1);
-  const size_t blockwide = 8 * (3 * ldn * n + 2 * ldn * m + 2 * ldm * n + 2 * ldm * m + 6 * (size_t)n + 4 * (size_t)m + (2 * n + m) + 16);
+  return 8 * (3 * ldn * n + 2 * ldn * m + 2 * ldm * n + 2 * ldm * m + 6 * (size_t)n + 4 * (size_t)m + (2 * n + m) + 16);
+}
+inline size_t cta_smem_bytes(int n, int m) {
+  const size_t blockwide = cta_blockwide_smem_bytes(n, m);
   const size_t warpwide = cta_is_small(n, m) ? cta_small_smem_bytes(n, m) : 0;  // the two plans overlay each other
   return blockwide > warpwide ? blockwide : warpwide;
 }
@@ -400,14 +405,16 @@ __device__ __forceinline__ void cta_unstage(double* dst, const double* src, int 
 // ---------------------------------------------------------------------------------------------
 // SolverDDP::calcDiff (ddp.cpp:157-178) for one problem: calc (only when do_calc: iter_ == 0), calcDiff of all
 // nodes, total cost in the reference's order (shooting.hxx:188-192) and the gaps fs. Returns the cost to all.
-template <class M>
+template <class M, bool nodes_done = false>
 __device__ double cta_calcdiff(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, int cur, bool do_calc,
                                bool is_feasible, bool was_feasible) {
   const int T = c.T, n = c.n, m = c.m;
   const double* xs = c.xs[cur] + (size_t)b * (T + 1) * n;
   const double* us = c.us[cur] + (size_t)b * T * m;
-  if (do_calc) mod.calc_all(c, b, xs, us);
-  mod.calcdiff_all(c, b, xs, us);
+  if constexpr (!nodes_done) {  // else: evaluated by cta_phase_nodes_kernel in an earlier launch
+    if (do_calc) mod.calc_all(c, b, xs, us);
+    mod.calcdiff_all(c, b, xs, us);
+  }
   __syncthreads();
   if (threadIdx.x == 0) {
     double cost = 0.;
@@ -885,8 +892,27 @@ static __global__ void cta_phase_init_kernel(const __grid_constant__ CtaCtx c, i
   CTA_I(I_PHASE) = maxiter > 0 ? 0 : 2;
 }
 
+// calc (first iteration only) + calcDiff of every node of every problem whose next step is computeDirection(recalc =
+// true): one thread per (problem, node) pair over the whole batch, so a lone problem gets T + 1 threads instead of one
+// warp's four passes and every warp is full (T + 1 = 101 = 3 x 32 + 5 otherwise)
 template <class M>
-__global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_phase_direction_kernel(const __grid_constant__ CtaCtx c, int* active) {
+__global__ void __launch_bounds__(64) cta_phase_nodes_kernel(const __grid_constant__ CtaCtx c) {
+  const int nt = c.T + 1;
+  const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (long)c.B * nt) return;
+  const int b = (int)(g / nt), t = (int)(g % nt);
+  if (CTA_I(I_PHASE) != 0 || !(CTA_I(I_LOOP) & 1)) return;
+  M mod;
+  mod.load(c, b);
+  const int cur = CTA_I(I_CUR);
+  const double* xs = c.xs[cur] + (size_t)b * nt * c.n;
+  const double* us = c.us[cur] + (size_t)b * c.T * c.m;
+  if (CTA_I(I_ITER) == 0) mod.calc_node(c, b, t, xs, us);
+  mod.calcdiff_node(c, b, t, xs, us);
+}
+
+template <class M>
+__global__ void __launch_bounds__(M::kMaxThreads, M::kDirMinBlocks) cta_phase_direction_kernel(const __grid_constant__ CtaCtx c, int* active) {
   extern __shared__ double cta_smem_raw[];
   const int b = blockIdx.x;
   const int phase = CTA_I(I_PHASE);
@@ -902,7 +928,7 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_phase_direc
   double dg = CTA_S(S_DG), dq = CTA_S(S_DQ), stop = CTA_S(S_STOP);  // kept when the backward pass fails
   __syncthreads();
   double cost = 0.;
-  if (recalc) cost = cta_calcdiff(c, mod, sm, b, cur, iter == 0, feas, wasfeas);
+  if (recalc) cost = cta_calcdiff<M, M::kNodeKernel>(c, mod, sm, b, cur, iter == 0, feas, wasfeas);
   const int st = cta_backward(c, mod, sm, b, feas, xreg, ureg, dg, dq, stop);
   if (threadIdx.x != 0) return;
   if (recalc) CTA_S(S_COST) = cost;
@@ -928,7 +954,7 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_phase_direc
 }
 
 template <class M>
-__global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_phase_forward_kernel(const __grid_constant__ CtaCtx c, int maxiter) {
+__global__ void __launch_bounds__(M::kMaxThreads, M::kFwdMinBlocks) cta_phase_forward_kernel(const __grid_constant__ CtaCtx c, int maxiter) {
   extern __shared__ double cta_smem_raw[];
   const int b = blockIdx.x;
   if (CTA_I(I_PHASE) != 1) return;

@@ -202,8 +202,13 @@ struct CtaBackend : Backend {
         if (h_active[old] == 0) break;
       }
       CGX_CUDA(cudaMemsetAsync(d_active + slot, 0, sizeof(int), stream));
+      if constexpr (M::kNodeKernel) {
+        const long nodes = (long)c.B * (c.T + 1);
+        cta_phase_nodes_kernel<M><<<(unsigned)((nodes + 63) / 64), 64, 0, stream>>>(c);
+        ++last_launches;
+      }
       cta_phase_direction_kernel<M><<<c.B, threads, smem, stream>>>(c, d_active + slot);
-      cta_phase_forward_kernel<M><<<c.B, threads, smem, stream>>>(c, maxiter);
+      cta_phase_forward_kernel<M><<<c.B, threads, cta_blockwide_smem_bytes(c.n, c.m), stream>>>(c, maxiter);
       last_launches += 2;
       CGX_CUDA(cudaMemcpyAsync(h_active + slot, d_active + slot, sizeof(int), cudaMemcpyDeviceToHost, stream));
       CGX_CUDA(cudaEventRecord(ring_ev[slot], stream));

@@ -681,31 +681,67 @@ __device__ int cta_forward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, in
   double* ut_ = c.us[cur ^ 1] + (size_t)b * T * m;
   const double* fs = c.fs + (size_t)b * (T + 1) * n;
   const double* w = c.w + (size_t)b * (T + 1) * n;
+  // Models with compile-time node sizes (the arm): the next node's xs, fs, w, us, k, K are copied into shared memory
+  // with cp.async while the current node's dynamics are evaluated. The rollout is serial in t and only a few warps
+  // are resident per SM, so every global load in the loop is an exposed L2/HBM round trip otherwise (two per node).
+  constexpr bool PF = M::kN > 0;
+  constexpr int KN = M::kN, KM = M::kM;
+  constexpr int PFS = PF ? 3 * KN + 2 * KM + KM * KN : 1;
+  __shared__ double pf[2][PFS];
+  auto prefetch = [&](int t, int buf) {
+    double* d = pf[buf];
+    for (int i = tid; i < KN; i += P) {
+      cp_async8(d + i, xs + (size_t)t * KN + i);
+      cp_async8(d + KN + i, fs + (size_t)t * KN + i);
+      cp_async8(d + 2 * KN + i, w + (size_t)t * KN + i);
+    }
+    if (t < T) {
+      const double* Kt = c.K + ((size_t)b * T + t) * KM * KN;
+      for (int i = tid; i < KM; i += P) {
+        cp_async8(d + 3 * KN + i, us + (size_t)t * KM + i);
+        cp_async8(d + 3 * KN + KM + i, c.k + ((size_t)b * T + t) * KM + i);
+      }
+      for (int e = tid; e < KM * KN; e += P) cp_async8(d + 3 * KN + 2 * KM + e, Kt + e);
+    }
+  };
   double cost_try = 0., dv = 0.;  // thread 0
   for (int i = tid; i < n; i += P) sm.xn[i] = c.x0[(size_t)b * n + i];
+  if constexpr (PF) prefetch(0, 0);
   __syncthreads();
   for (int t = 0; t <= T; ++t) {
+    const double *xs_t = xs + (size_t)t * n, *fs_t = fs + (size_t)t * n, *w_t = w + (size_t)t * n;
+    const double *us_t = us + (size_t)t * m, *Kt = c.K + ((size_t)b * T + t) * m * n, *kt = c.k + ((size_t)b * T + t) * m;
+    if constexpr (PF) {
+      cp_async_wait_all();
+      __syncthreads();  // node t has landed for every thread; node t - 1's buffer is free again
+      const double* d = pf[t & 1];
+      xs_t = d;
+      fs_t = d + KN;
+      w_t = d + 2 * KN;
+      us_t = d + 3 * KN;
+      kt = d + 3 * KN + KM;
+      Kt = d + 3 * KN + 2 * KM;
+      if (t < T) prefetch(t + 1, (t + 1) & 1);
+    }
     for (int i = tid; i < n; i += P) {
-      const double xt = closed ? sm.xn[i] : sm.xn[i] + fs[(size_t)t * n + i] * am1;
+      const double xt = closed ? sm.xn[i] : sm.xn[i] + fs_t[i] * am1;
       sm.x[i] = xt;
-      sm.dx[i] = xt - xs[(size_t)t * n + i];
+      sm.dx[i] = xt - xs_t[i];
       xt_[(size_t)t * n + i] = xt;
     }
     __syncthreads();
     if (t < T) {
-      const double* Kt = c.K + ((size_t)b * T + t) * m * n;
-      const double* kt = c.k + ((size_t)b * T + t) * m;
       for (int i = tid; i < m; i += P) {
         double s = 0.;
         for (int j = 0; j < n; ++j) s += Kt[i + m * j] * sm.dx[j];
-        const double u = us[(size_t)t * m + i] - kt[i] * alpha - s;
+        const double u = us_t[i] - kt[i] * alpha - s;
         sm.u[i] = u;
         ut_[(size_t)t * m + i] = u;
       }
     }
     if (tid == 0 && use_w) {
       double s = 0.;
-      for (int i = 0; i < n; ++i) s += w[(size_t)t * n + i] * sm.dx[i];
+      for (int i = 0; i < n; ++i) s += w_t[i] * sm.dx[i];
       dv += s;
     }
     __syncthreads();
@@ -721,7 +757,10 @@ __device__ int cta_forward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, in
     }
     if (t < T)
       for (int i = tid; i < n; i += P) bad |= raise_if_nan(fabs(sm.xn[i]));
-    if (__syncthreads_or(bad)) return 1;
+    if (__syncthreads_or(bad)) {
+      if constexpr (PF) cp_async_wait_all();  // nothing in flight into shared memory when the caller moves on
+      return 1;
+    }
   }
   if (tid == 0) {
     sm.red[0] = cost_try;

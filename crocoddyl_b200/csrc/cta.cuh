@@ -666,9 +666,16 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, b
 // whole block, fused with SolverFDDP::expectedImprovement's gap term dv = sum_t w_t^T (xs_try_t - xs_t)
 // (fddp.cpp:107-124). Node data (xnext, cost) are overwritten by the trial exactly like the reference's datas.
 // Returns 0 or 1 ("forward_error") to all threads; cost_try and dv valid on every thread.
+// where a trial goes when it is not the problem's own trial buffers (concurrent line search): whole-batch arrays
+struct TrialBufs {
+  double* xs;     // [B][T+1][n]
+  double* us;     // [B][T][m]
+  double* xnext;  // [B][T+1][n]
+  double* cost;   // [B][T+1]
+};
 template <class M>
 __device__ int cta_forward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, int cur, double alpha, bool is_feasible,
-                           double& cost_try_out, double& dv_out) {
+                           double& cost_try_out, double& dv_out, const TrialBufs* tb = nullptr) {
   const int T = c.T, n = c.n, m = c.m;
   const int tid = threadIdx.x, P = blockDim.x;
   const bool fddp = c.fddp != 0;
@@ -677,8 +684,10 @@ __device__ int cta_forward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, in
   const double am1 = alpha - 1.;
   const double* xs = c.xs[cur] + (size_t)b * (T + 1) * n;
   const double* us = c.us[cur] + (size_t)b * T * m;
-  double* xt_ = c.xs[cur ^ 1] + (size_t)b * (T + 1) * n;
-  double* ut_ = c.us[cur ^ 1] + (size_t)b * T * m;
+  double* xt_ = (tb ? tb->xs : c.xs[cur ^ 1]) + (size_t)b * (T + 1) * n;
+  double* ut_ = (tb ? tb->us : c.us[cur ^ 1]) + (size_t)b * T * m;
+  double* xnext_ = tb ? tb->xnext : c.d_xnext;
+  double* cost_ = tb ? tb->cost : c.d_cost;
   const double* fs = c.fs + (size_t)b * (T + 1) * n;
   const double* w = c.w + (size_t)b * (T + 1) * n;
   // Models with compile-time node sizes (the arm): the next node's xs, fs, w, us, k, K are copied into shared memory
@@ -748,10 +757,10 @@ __device__ int cta_forward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, in
     mod.calc_block(sm.x, t < T ? sm.u : nullptr, sm.xn, sm.scr, &sm.red[3]);
     // datas[t]->xnext / cost (overwritten by every trial)
     const size_t node = (size_t)b * (T + 1) + t;
-    for (int i = tid; i < n; i += P) c.d_xnext[node * n + i] = sm.xn[i];
+    for (int i = tid; i < n; i += P) xnext_[node * n + i] = sm.xn[i];
     int bad = 0;
     if (tid == 0) {
-      c.d_cost[node] = sm.red[3];
+      cost_[node] = sm.red[3];
       cost_try += sm.red[3];
       bad = raise_if_nan(cost_try);
     }
@@ -910,6 +919,7 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_solve_kerne
 // the same device functions in the same order, so results are identical to the fused kernel.
 //   cta_phase_direction_kernel : problems in phase 0 — computeDirection incl. ONE regularisation retry per launch
 //   cta_phase_forward_kernel   : problems in phase 1 — ONE trial of the line search + the end-of-iteration bookkeeping
+//   cta_phase_forward_wide_kernel + cta_phase_select_kernel : the same with CTA_LS_WIDTH trials at once (tail of a batch)
 static __global__ void cta_phase_init_kernel(const __grid_constant__ CtaCtx c, int maxiter, int is_feasible0, double reginit) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= c.B) return;
@@ -992,32 +1002,26 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kDirMinBlocks) cta_phase_di
   CTA_I(I_PHASE) = 1;
 }
 
-template <class M>
-__global__ void __launch_bounds__(M::kMaxThreads, M::kFwdMinBlocks) cta_phase_forward_kernel(const __grid_constant__ CtaCtx c, int maxiter) {
-  extern __shared__ double cta_smem_raw[];
-  const int b = blockIdx.x;
-  if (CTA_I(I_PHASE) != 1) return;
-  CtaSmem sm;
-  sm.carve(cta_smem_raw, c.n, c.m);
-  M mod;
-  mod.load(c, b);
+// What SolverDDP/FDDP::solve does with the result of ONE trial of the line search (ddp.cpp:72-116, fddp.cpp:56-103),
+// by one thread: the acceptance test, and — when the step is accepted or the step lengths are exhausted — the end of
+// the iteration (regularisation update, trace record, stopping test). st / cost_try / dv: what cta_forward returned for
+// step length index I_ALPHA. Leaves I_PHASE = 1 with I_ALPHA advanced when the next step length has to be tried.
+__device__ inline void cta_phase_trial_done(const CtaCtx& c, int b, int maxiter, int st, double cost_try_new, double dv) {
   const bool fddp = c.fddp != 0;
   int cur = CTA_I(I_CUR);
   bool feas = CTA_I(I_FEAS) != 0, wasfeas = CTA_I(I_WASFEAS) != 0;
   const int a = CTA_I(I_ALPHA);
   const double steplength = c.o.alphas[a];
-  double cost = CTA_S(S_COST), cost_try = CTA_S(S_COST_TRY), d0 = CTA_S(S_D0), d1 = CTA_S(S_D1);
+  double cost = CTA_S(S_COST), d0 = CTA_S(S_D0), d1 = CTA_S(S_D1);
   double dV = CTA_S(S_DV), dVexp = CTA_S(S_DVEXP);
   const double dg = CTA_S(S_DG), dq = CTA_S(S_DQ), stop = CTA_S(S_STOP);
   double xreg = CTA_S(S_XREG), ureg = CTA_S(S_UREG);
-  __syncthreads();
-  double dv = 0.;
-  const int st = cta_forward(c, mod, sm, b, cur, steplength, feas, cost_try, dv);
-  if (threadIdx.x != 0) return;
   ++CTA_I(I_NFWD);
   int accepted = -1;
   bool recalc = false;
   if (!st) {
+    const double cost_try = cost_try_new;
+    CTA_S(S_COST_TRY) = cost_try;
     dV = cost - cost_try;
     if (fddp) {
       d0 = dg + dv;
@@ -1034,12 +1038,11 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kFwdMinBlocks) cta_phase_fo
     }
   }
   CTA_S(S_STEP) = steplength;
-  CTA_S(S_COST_TRY) = cost_try;
   CTA_S(S_DV) = dV;
   CTA_S(S_DVEXP) = dVexp;
   CTA_S(S_D0) = d0;
   CTA_S(S_D1) = d1;
-  if (accepted < 0 && a + 1 < c.o.nalphas) {  // next step length at the next launch
+  if (accepted < 0 && a + 1 < c.o.nalphas) {  // next step length
     CTA_I(I_ALPHA) = a + 1;
     return;
   }
@@ -1088,6 +1091,94 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kFwdMinBlocks) cta_phase_fo
   CTA_I(I_ITER) = iter;
   CTA_I(I_RETRIES) = 0;
   CTA_I(I_PHASE) = done ? 2 : 0;
+}
+
+template <class M>
+__global__ void __launch_bounds__(M::kMaxThreads, M::kFwdMinBlocks) cta_phase_forward_kernel(const __grid_constant__ CtaCtx c, int maxiter) {
+  extern __shared__ double cta_smem_raw[];
+  const int b = blockIdx.x;
+  if (CTA_I(I_PHASE) != 1) return;
+  CtaSmem sm;
+  sm.carve(cta_smem_raw, c.n, c.m);
+  M mod;
+  mod.load(c, b);
+  const int cur = CTA_I(I_CUR);
+  const bool feas = CTA_I(I_FEAS) != 0;
+  const double steplength = c.o.alphas[CTA_I(I_ALPHA)];
+  __syncthreads();
+  double cost_try = 0., dv = 0.;
+  const int st = cta_forward(c, mod, sm, b, cur, steplength, feas, cost_try, dv);
+  if (threadIdx.x == 0) cta_phase_trial_done(c, b, maxiter, st, cost_try, dv);
+}
+
+// Concurrent line search (the trials of one iteration are independent given xs, us, K, k): block (b, g)
+// rolls out step length index I_ALPHA + g of problem b. Slot 0 writes the problem's own trial buffers, slot g > 0 the
+// g-th spare set; nothing of the solver state changes here. cta_phase_select_kernel then walks the slots in the
+// reference's order, so the accepted step, the counters and the trace are those of the sequential search; the
+// trajectories and node data of the slot the search ended on become the problem's trial. Used by the host while the
+// unfinished problems x width fit the GPU in one wave (the tail of a batch), where it shortens the critical path of
+// the slowest problems from (trials) to (1) rollouts per iteration; with the machine full it would only add work.
+constexpr int CTA_LS_WIDTH = 4;
+struct TrialSlots {
+  TrialBufs spare[CTA_LS_WIDTH - 1];
+  double* res;  // [CTA_LS_WIDTH][3][Bp]: status, cost_try, dv of every slot
+};
+template <class M>
+__global__ void __launch_bounds__(M::kMaxThreads, M::kFwdMinBlocks) cta_phase_forward_wide_kernel(const __grid_constant__ CtaCtx c, const __grid_constant__ TrialSlots ts) {
+  extern __shared__ double cta_smem_raw[];
+  const int b = blockIdx.x, g = blockIdx.y;
+  if (CTA_I(I_PHASE) != 1) return;
+  const int a = CTA_I(I_ALPHA) + g;
+  if (a >= c.o.nalphas) return;
+  CtaSmem sm;
+  sm.carve(cta_smem_raw, c.n, c.m);
+  M mod;
+  mod.load(c, b);
+  const int cur = CTA_I(I_CUR);
+  const bool feas = CTA_I(I_FEAS) != 0;
+  const double steplength = c.o.alphas[a];
+  __syncthreads();
+  double cost_try = 0., dv = 0.;
+  const int st = cta_forward(c, mod, sm, b, cur, steplength, feas, cost_try, dv, g ? &ts.spare[g - 1] : nullptr);
+  if (threadIdx.x == 0) {
+    double* r = ts.res + (size_t)g * 3 * c.Bp;
+    r[b] = st;
+    r[(size_t)c.Bp + b] = cost_try;
+    r[(size_t)2 * c.Bp + b] = dv;
+  }
+}
+static __global__ void cta_phase_select_kernel(const __grid_constant__ CtaCtx c, const __grid_constant__ TrialSlots ts, int maxiter) {
+  const int b = blockIdx.x;
+  __shared__ int s_slot, s_cur;
+  if (CTA_I(I_PHASE) != 1) return;
+  __syncthreads();  // every thread has seen phase 1 before thread 0 changes it
+  if (threadIdx.x == 0) {
+    s_cur = CTA_I(I_CUR);
+    int slot = -1;
+    for (int g = 0; g < CTA_LS_WIDTH; ++g) {
+      if (CTA_I(I_ALPHA) >= c.o.nalphas) break;
+      const double* r = ts.res + (size_t)g * 3 * c.Bp;
+      cta_phase_trial_done(c, b, maxiter, (int)r[b], r[(size_t)c.Bp + b], r[(size_t)2 * c.Bp + b]);
+      if (CTA_I(I_PHASE) != 1) {  // the iteration ended on this slot
+        slot = g;
+        break;
+      }
+    }
+    s_slot = slot;
+  }
+  __syncthreads();
+  const int slot = s_slot;
+  if (slot <= 0) return;  // slot 0 is the problem's own trial buffers; -1: the search goes on
+  const size_t T = c.T, n = c.n, m = c.m;
+  const TrialBufs& sp = ts.spare[slot - 1];
+  double* xt = c.xs[s_cur ^ 1] + (size_t)b * (T + 1) * n;
+  double* ut = c.us[s_cur ^ 1] + (size_t)b * T * m;
+  for (size_t e = threadIdx.x; e < (T + 1) * n; e += blockDim.x) {
+    xt[e] = sp.xs[(size_t)b * (T + 1) * n + e];
+    c.d_xnext[(size_t)b * (T + 1) * n + e] = sp.xnext[(size_t)b * (T + 1) * n + e];
+  }
+  for (size_t e = threadIdx.x; e < T * m; e += blockDim.x) ut[e] = sp.us[(size_t)b * T * m + e];
+  for (size_t e = threadIdx.x; e <= T; e += blockDim.x) c.d_cost[(size_t)b * (T + 1) + e] = sp.cost[(size_t)b * (T + 1) + e];
 }
 
 // ---------------------------------------------------------------------------------------------

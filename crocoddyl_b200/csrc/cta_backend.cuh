@@ -19,6 +19,9 @@ struct CtaBackend : Backend {
   int threads = 128;
   size_t smem = 0;
   bool phase_split = M::kPhaseSplit;  // CGX_CTA_FUSED=1 / CGX_CTA_PHASES=1 override (development A/B knob)
+  TrialSlots slots;       // spare trial buffers of the concurrent line search (allocated on first use)
+  int wide_mode = -1;     // -1 automatic, 0 never, 1 always (CGX_CTA_WIDE, development / test knob)
+  int num_sms = 148;
   int* d_active = nullptr;
   int* h_active = nullptr;
   cudaEvent_t ring_ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -53,6 +56,10 @@ struct CtaBackend : Backend {
     CGX_CUDA(cudaFuncSetAttribute(cta_solve_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CGX_CUDA(cudaFuncSetAttribute(cta_phase_direction_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CGX_CUDA(cudaFuncSetAttribute(cta_phase_forward_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CGX_CUDA(cudaFuncSetAttribute(cta_phase_forward_wide_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    std::memset(&slots, 0, sizeof(slots));
+    CGX_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+    if (const char* e = getenv("CGX_CTA_WIDE")) wide_mode = atoi(e);
     if (const char* e = getenv("CGX_CTA_FUSED")) if (e[0] == '1') phase_split = false;
     if (const char* e = getenv("CGX_CTA_PHASES")) if (e[0] == '1') phase_split = true;
     CGX_CUDA(cudaFuncSetAttribute(cta_direction_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -179,6 +186,17 @@ struct CtaBackend : Backend {
     CGX_CUDA(cudaEventRecord(ev[2], stream));
     CGX_CUDA(cudaGetLastError());
   }
+  void ensure_trial_slots() {
+    if (slots.res) return;
+    const size_t B = c.B, T = c.T, n = c.n, m = c.m;
+    for (int g = 0; g < CTA_LS_WIDTH - 1; ++g) {
+      slots.spare[g].xs = alloc(B * (T + 1) * n);
+      slots.spare[g].us = alloc(B * T * m);
+      slots.spare[g].xnext = alloc(B * (T + 1) * n);
+      slots.spare[g].cost = alloc(B * (T + 1));
+    }
+    slots.res = alloc((size_t)CTA_LS_WIDTH * 3 * c.Bp);
+  }
   // Phase-split solve (cta.cuh): alternate the direction and the line-search launches over the whole batch until every
   // problem has returned. The count of unfinished problems a direction launch saw comes back through pinned memory
   // two rounds late, so the host never stalls the stream; the two surplus rounds are empty launches.
@@ -194,13 +212,18 @@ struct CtaBackend : Backend {
     ++last_launches;
     // upper bound of rounds: every round an unfinished problem either runs a backward pass or a trial
     const long max_rounds = (long)maxiter * (c.o.nalphas + 64) + RING;
+    long unfinished = c.B;  // last count that came back (never smaller than the truth)
     for (long r = 0; r < max_rounds; ++r) {
       const int slot = (int)(r % RING);
       if (r >= RING - 1) {  // result of round r - (RING - 1)
         const int old = (int)((r - (RING - 1)) % RING);
         CGX_CUDA(cudaEventSynchronize(ring_ev[old]));
         if (h_active[old] == 0) break;
+        unfinished = h_active[old];
       }
+      // concurrent line search while all trials of the unfinished problems fit the GPU in one wave (cta.cuh)
+      const bool wide = wide_mode == 1 || (wide_mode < 0 && unfinished * CTA_LS_WIDTH <= (long)num_sms * M::kFwdMinBlocks);
+      if (wide) ensure_trial_slots();
       CGX_CUDA(cudaMemsetAsync(d_active + slot, 0, sizeof(int), stream));
       if constexpr (M::kNodeKernel) {
         const long nodes = (long)c.B * (c.T + 1);
@@ -208,7 +231,13 @@ struct CtaBackend : Backend {
         ++last_launches;
       }
       cta_phase_direction_kernel<M><<<c.B, threads, smem, stream>>>(c, d_active + slot);
-      cta_phase_forward_kernel<M><<<c.B, threads, cta_blockwide_smem_bytes(c.n, c.m), stream>>>(c, maxiter);
+      if (wide) {
+        cta_phase_forward_wide_kernel<M><<<dim3(c.B, CTA_LS_WIDTH), threads, cta_blockwide_smem_bytes(c.n, c.m), stream>>>(c, slots);
+        cta_phase_select_kernel<<<c.B, 128, 0, stream>>>(c, slots, maxiter);
+        ++last_launches;
+      } else {
+        cta_phase_forward_kernel<M><<<c.B, threads, cta_blockwide_smem_bytes(c.n, c.m), stream>>>(c, maxiter);
+      }
       last_launches += 2;
       CGX_CUDA(cudaMemcpyAsync(h_active + slot, d_active + slot, sizeof(int), cudaMemcpyDeviceToHost, stream));
       CGX_CUDA(cudaEventRecord(ring_ev[slot], stream));

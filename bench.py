@@ -76,9 +76,14 @@ class Arm(object):
     xReg 1e-4, uReg 1e-4; q ~ U(-1,1)^7, v = 0, seed 2; init_us = quasiStatic(x0); reginit 0.1."""
     name, nx, nu, reginit = "arm", 14, 7, 0.1
     default_batch, cpu_sample = 1024, 256
-    kernel = "cta_solve_kernel<ArmModel<7>>"
+    kernel = ("cta_phase_{nodes,direction,forward}_kernel<ArmModel<7>>: one solve = lockstep rounds of calc/calcDiff, "
+              "backward pass and line-search launches over the whole batch (kernel_ms = the whole sequence)")
     oracle_kind = "arm"
     n, m = 14, 7
+    # FP64 work per node (SURVEY 8d): Riccati F_ric(14,7); calc / calcDiff = static operation count of the node functions
+    # (tools/count_fp64_ops.py: DFMA = 2, DADD = DMUL = 1 flop)
+    flops_ric = 4 * n**3 + 6 * n * n * m + 4 * n * m * m + m**3 / 3. + 6 * n * n + 6 * n * m + 4 * m * m
+    flops_calc, flops_calcdiff = 7375., 22173.
     # CTA-per-problem core: node derivatives are written by calcDiff and read back by the backward pass
     bytes_bwd = 8 * ((n + m) + 2 * (2 * n * n + n * m + m * m + n + m) + n + m * n + m + 2 * n + n * n)
     bytes_fwd = 8 * (n + m + m * n + m + n + n + n + m + n + 1)
@@ -392,6 +397,15 @@ def main():
                          "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": kms},
         }
+        if hasattr(wl, "flops_ric"):  # arm: the FP64 view of the same step (north_star: Riccati / ABA-derivative kernels)
+            nrec = sg["n_records"]
+            flops = float((T * nb * wl.flops_ric + (T + 1) * ((nrec + 1) * wl.flops_calcdiff + (nf + 1) * wl.flops_calc)).sum())
+            fp64_peak = cb.probe_fp64_tflops()
+            line["fp64"] = {"achieved": flops / (kms * 1e-3) / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
+                            "frac": flops / (kms * 1e-3) / 1e12 / fp64_peak,
+                            "peak_source": "measured on this GPU (cgx_probe_fp64_tflops, register-resident DFMA loop)",
+                            "algorithmic_flops_per_step": flops,
+                            "note": "upper bound of calcDiff evaluations: one per accepted iteration + the first"}
         if not args.no_cpu_baseline:
             nsample = wl.cpu_sample
             rate, cores, sec = cpu_oracle_rate(wl, nsample)

@@ -47,6 +47,9 @@ struct CtaBackend : Backend {
     threads = ((tn * tn + 31) / 32) * 32;
     if (threads < M::kMinThreads) threads = M::kMinThreads;
     if (threads > M::kMaxThreads) threads = M::kMaxThreads;
+    // small nodes: the backward pass is one warp's work (cta_small.cuh), a second warp only halves the resident
+    // problems per SM (measured, LQR n = 12, B = 4096: see profiles/r01_riccati_sweep_v3.json)
+    if (cta_is_small(c.n, c.m)) threads = 32;
     smem = cta_smem_bytes(c.n, c.m);
     int dev = 0, maxsm = 0;
     CGX_CUDA(cudaGetDevice(&dev));

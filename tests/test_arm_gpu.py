@@ -177,3 +177,49 @@ def test_config_c4_full_horizon_sampled_against_oracle():
     _close(sg["cost"][:NS], so["cost"], "cost")
     _close(xg[:NS], ob.get_all("xs"), "xs", 1e-7)
     _close(ug[:NS], ob.get_all("us"), "us", 1e-7)
+
+
+def _solve_in_mode(env, solver_kind, model, x0, xs, T, maxiter=100):
+    """One batched solve with the development knobs of the CTA backend set (read when the solver is created)."""
+    import os
+    keys = ("CGX_CTA_FUSED", "CGX_CTA_PHASES", "CGX_CTA_WIDE")
+    old = {k: os.environ.pop(k, None) for k in keys}
+    os.environ.update(env)
+    try:
+        problem = cb.ShootingProblem(x0, [model] * T, model.terminal_model)
+        us = np.repeat(problem.quasiStatic(x0)[:, None, :], T, 1)
+        solver = (cb.SolverFDDP if solver_kind == "fddp" else cb.SolverDDP)(problem)
+        solver.enableTrace(maxiter + 1)
+        solver.solve(xs, us, maxiter, False, 0.1)
+        out = {"sc": solver.scalars(), "tr": [solver.trace(b) for b in range(x0.shape[0])]}
+        for f in ("xs", "us", "K", "k", "Vx", "Vxx"):
+            out[f] = solver.get(f)
+        return out
+    finally:
+        for k in keys:
+            os.environ.pop(k, None)
+            if old[k] is not None:
+                os.environ[k] = old[k]
+
+
+@pytest.mark.parametrize("solver_kind", ["fddp", "ddp"])
+def test_phase_split_and_concurrent_line_search_equal_the_fused_loop(solver_kind):
+    """The three schedules of the same solve loop — fused per-problem kernel, lockstep phase launches with a
+    sequential line search, and phase launches with 4 step lengths rolled out at once — must make identical
+    decisions (iterations, accepted step length, regularisation, counters) and leave the same iterates."""
+    model = _model("synthetic", 7)
+    B, T = 48, 25
+    x0, xs = _c4_inputs(model, B, T, seed=3)
+    ref = _solve_in_mode({"CGX_CTA_FUSED": "1"}, solver_kind, model, x0, xs, T)
+    assert ref["sc"]["n_forward"].max() > ref["sc"]["n_backward"].max()  # the case does reject step lengths
+    for env in ({"CGX_CTA_WIDE": "0"}, {"CGX_CTA_WIDE": "1"}, {}):
+        got = _solve_in_mode(env, solver_kind, model, x0, xs, T)
+        for k in ("iter", "converged", "n_records", "n_backward", "n_forward", "is_feasible", "xreg", "steplength"):
+            assert np.array_equal(got["sc"][k], ref["sc"][k]), (env, k)
+        for b in range(B):
+            assert got["tr"][b].shape == ref["tr"][b].shape, (env, b)
+            for col in (0, 5, 6, 7, 8, 11, 12):
+                assert np.array_equal(got["tr"][b][:, col], ref["tr"][b][:, col]), (env, b, col)
+        _close(got["sc"]["cost"], ref["sc"]["cost"], "cost", 1e-12)
+        for f in ("xs", "us", "K", "k", "Vx", "Vxx"):
+            _close(got[f], ref[f], f, 1e-10)

@@ -211,7 +211,7 @@ def test_phase_split_and_concurrent_line_search_equal_the_fused_loop(solver_kind
     B, T = 48, 25
     x0, xs = _c4_inputs(model, B, T, seed=3)
     ref = _solve_in_mode({"CGX_CTA_FUSED": "1"}, solver_kind, model, x0, xs, T)
-    assert ref["sc"]["n_forward"].max() > ref["sc"]["n_backward"].max()  # the case does reject step lengths
+    assert (ref["sc"]["n_forward"] > ref["sc"]["n_backward"]).any()  # the case does reject step lengths
     for env in ({"CGX_CTA_WIDE": "0"}, {"CGX_CTA_WIDE": "1"}, {}):
         got = _solve_in_mode(env, solver_kind, model, x0, xs, T)
         for k in ("iter", "converged", "n_records", "n_backward", "n_forward", "is_feasible", "xreg", "steplength"):

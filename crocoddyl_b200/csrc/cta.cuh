@@ -941,11 +941,14 @@ static __global__ void cta_phase_init_kernel(const __grid_constant__ CtaCtx c, i
   CTA_I(I_PHASE) = maxiter > 0 ? 0 : 2;
 }
 
+#ifndef CGX_NODES_MINBLOCKS
+#define CGX_NODES_MINBLOCKS 4
+#endif
 // calc (first iteration only) + calcDiff of every node of every problem whose next step is computeDirection(recalc =
 // true): one thread per (problem, node) pair over the whole batch, so a lone problem gets T + 1 threads instead of one
 // warp's four passes and every warp is full (T + 1 = 101 = 3 x 32 + 5 otherwise)
 template <class M>
-__global__ void __launch_bounds__(64) cta_phase_nodes_kernel(const __grid_constant__ CtaCtx c) {
+__global__ void __launch_bounds__(64, CGX_NODES_MINBLOCKS) cta_phase_nodes_kernel(const __grid_constant__ CtaCtx c) {
   const int nt = c.T + 1;
   const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= (long)c.B * nt) return;

@@ -153,6 +153,14 @@ int orc_batch_set(void* h, const char* name, double v) {
   return 0;
 }
 
+// SolverDDP::set_alphas (ddp.cpp:444-462): the list replaces alphas_; thresholds are left alone
+int orc_batch_set_alphas(void* h, const double* alphas, int n) {
+  Batch* bt = (Batch*)h;
+  if (n <= 0) return -1;
+  for (auto& s : bt->solvers) s->alphas.assign(alphas, alphas + n);
+  return 0;
+}
+
 // init_xs: B*(T+1)*nx or NULL (=> state zero, solver-base.cpp:46-50); init_us: B*T*nu or NULL (zeros).
 // Returns number of converged problems; converged[b] readable via orc_batch_scalars. seconds_out (optional)
 // receives the CLOCK_MONOTONIC wall time of the parallel region (reference clock: core/utils/timer.hpp:17-43).

@@ -32,6 +32,7 @@ def load(fast=False):
     lib.orc_batch_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _dp, C.c_long, C.c_int, _dp]
     lib.orc_batch_destroy.argtypes = [C.c_void_p]
     lib.orc_batch_set.argtypes = [C.c_void_p, C.c_char_p, C.c_double]
+    lib.orc_batch_set_alphas.argtypes = [C.c_void_p, _dp, C.c_int]
     lib.orc_batch_solve.argtypes = [C.c_void_p, _dp, _dp, C.c_int, C.c_int, C.c_double, C.c_int, _dp]
     lib.orc_batch_set_candidate.argtypes = [C.c_void_p, _dp, _dp, C.c_int]
     lib.orc_batch_calc.argtypes = [C.c_void_p, _dp]
@@ -71,6 +72,10 @@ class OracleBatch:
 
     def set(self, name, v):
         assert self.lib.orc_batch_set(self.h, name.encode(), float(v)) == 0
+
+    def set_alphas(self, alphas):
+        a = np.ascontiguousarray(alphas, dtype=np.float64)
+        assert self.lib.orc_batch_set_alphas(self.h, _p(a), a.size) == 0
 
     def solve(self, init_xs=None, init_us=None, maxiter=100, is_feasible=False, reginit=1e-9, nthreads=0):
         xs = None if init_xs is None else np.ascontiguousarray(init_xs, dtype=np.float64)

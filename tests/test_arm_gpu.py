@@ -223,3 +223,49 @@ def test_phase_split_and_concurrent_line_search_equal_the_fused_loop(solver_kind
         _close(got["sc"]["cost"], ref["sc"]["cost"], "cost", 1e-12)
         for f in ("xs", "us", "K", "k", "Vx", "Vxx"):
             _close(got[f], ref[f], f, 1e-10)
+
+
+@pytest.mark.parametrize("alphas", [[1.0], [1.0, 0.5], [1.0, 0.5, 0.25, 0.125, 0.0625], [1.0, 0.7, 0.3, 0.1, 0.05, 0.01, 1e-3]])
+def test_concurrent_line_search_with_other_step_length_lists(alphas):
+    """SolverDDP::set_alphas (ddp.cpp:444-462) with fewer / more step lengths than the 4 slots of the concurrent line
+    search (small batches run it from the first round): same decisions and iterates as the oracle."""
+    model = _model("synthetic", 7)
+    B, T = 10, 20
+    x0, xs = _c4_inputs(model, B, T, seed=5)
+    problem, solver, ob = _pair("fddp", model, x0, T)
+    us = np.repeat(problem.quasiStatic(x0)[:, None, :], T, 1)
+    solver.alphas = alphas
+    ob.set_alphas(alphas)
+    solver.enableTrace(40)
+    conv = solver.solve(xs, us, 30, False, 0.1)
+    ob.solve(xs, us, 30, False, 0.1)
+    _compare_solve(solver, ob, conv, rtol=1e-7)
+    sg, so = solver.scalars(), ob.scalars()
+    assert np.array_equal(sg["steplength"], so["steplength"])
+    for b in range(B):
+        tg, to = solver.trace(b), ob.trace(b)
+        assert tg.shape == to.shape
+        for col in (0, 5, 6, 7, 8, 11, 12):
+            assert np.array_equal(tg[:, col], to[:, col]), (b, col)
+
+
+@pytest.mark.parametrize("maxiter,feasible", [(0, False), (1, False), (3, True)])
+def test_phase_split_solve_small_iteration_budgets(maxiter, feasible):
+    """maxiter = 0 returns the candidate untouched, maxiter = 1 is the reference benchmark's call
+    (benchmark/arm-manipulation-optctrl.cpp:61), and a feasible (rolled-out) start takes the closed-gap branches."""
+    model = _model("synthetic", 7)
+    B, T = 5, 15
+    x0, xs = _c4_inputs(model, B, T, seed=8)
+    problem, solver, ob = _pair("fddp", model, x0, T)
+    us = np.repeat(problem.quasiStatic(x0)[:, None, :], T, 1)
+    if feasible:
+        xs = problem.rollout(us)
+    conv = solver.solve(xs, us, maxiter, feasible, 0.1)
+    ob.solve(xs, us, maxiter, feasible, 0.1)
+    sg, so = solver.scalars(), ob.scalars()
+    assert np.array_equal(sg["iter"], so["iter"]) and np.array_equal(sg["n_records"], so["n_records"])
+    assert np.array_equal(np.atleast_1d(conv), so["converged"].astype(bool))
+    _close(solver.get("xs"), ob.get_all("xs"), "xs", 1e-9)
+    _close(solver.get("us"), ob.get_all("us"), "us", 1e-9)
+    if maxiter:
+        _close(sg["cost"], so["cost"], "cost", 1e-9)

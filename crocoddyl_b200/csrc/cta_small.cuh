@@ -293,7 +293,65 @@ __device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, bool is_f
         if (lane < n) c.Qx[rnode * n + lane] = Qx[lane];
         if (lane < m) c.Qu[rnode * m + lane] = Qu[lane];
       }
-      // P3: computeGains (ddp.cpp:298-310): unblocked lower LLT, lane i owns row i
+      // P3 + P4: computeGains (ddp.cpp:298-310): unblocked lower LLT of Quu, then K = Quu^-1 Qxu^T, k = Quu^-1 Qu.
+      if constexpr (KM > 0) {
+        // Compile-time m: EVERY lane factorises Quu redundantly in registers — no barriers and no shared-memory round
+        // trips inside the serial chain — keeps the reciprocal pivots, and solves its own right-hand side in registers.
+        // (ncu source page of the shared-memory version below: 36 % of the backward kernel's samples in these lines.)
+        // Same operation order as Eigen's unblocked LLT / the oracle; x / p becomes x * (1 / p) (<= 1 ulp).
+        constexpr int NLR = KM * (KM + 1) / 2;
+        double Lr[NLR], rinv[KM];
+#pragma unroll
+        for (int i = 0; i < KM; ++i)
+#pragma unroll
+          for (int j = 0; j <= i; ++j) Lr[i * (i + 1) / 2 + j] = Lc[i + ldm * j];
+        bool notpd = false;
+#pragma unroll
+        for (int kk = 0; kk < KM; ++kk) {
+          double p = Lr[kk * (kk + 1) / 2 + kk];
+#pragma unroll
+          for (int j = 0; j < kk; ++j) p -= Lr[kk * (kk + 1) / 2 + j] * Lr[kk * (kk + 1) / 2 + j];
+          if (p <= 0.) notpd = true;  // a NaN pivot does not fail here; raiseIfNaN catches it below
+          p = sqrt(p);
+          const double pinv = 1. / p;
+          Lr[kk * (kk + 1) / 2 + kk] = p;
+          rinv[kk] = pinv;
+#pragma unroll
+          for (int i = kk + 1; i < KM; ++i) {
+            double sv = Lr[i * (i + 1) / 2 + kk];
+#pragma unroll
+            for (int j = 0; j < kk; ++j) sv -= Lr[i * (i + 1) / 2 + j] * Lr[kk * (kk + 1) / 2 + j];
+            Lr[i * (i + 1) / 2 + kk] = sv * pinv;
+          }
+        }
+        if (notpd) {
+          status = 1;
+          break;
+        }
+        if (lane <= n) {
+          double rr[KM];
+#pragma unroll
+          for (int i = 0; i < KM; ++i) rr[i] = (lane < n) ? Qxu[lane + ldn * i] : Qu[i];
+#pragma unroll
+          for (int i = 0; i < KM; ++i) {
+            double sv = rr[i];
+#pragma unroll
+            for (int j = 0; j < i; ++j) sv -= Lr[i * (i + 1) / 2 + j] * rr[j];
+            rr[i] = sv * rinv[i];
+          }
+#pragma unroll
+          for (int i = KM - 1; i >= 0; --i) {
+            double sv = rr[i];
+#pragma unroll
+            for (int j = i + 1; j < KM; ++j) sv -= Lr[j * (j + 1) / 2 + i] * rr[j];
+            rr[i] = sv * rinv[i];
+          }
+          double* r = (lane < n) ? (Kg + ldm * lane) : kg;
+#pragma unroll
+          for (int i = 0; i < KM; ++i) r[i] = rr[i];
+        }
+      } else {
+      // run-time m: unblocked lower LLT in shared memory, lane i owns row i
       for (int kk = 0; kk < m; ++kk) {
         double p = Lc[kk + ldm * kk];
         for (int j = 0; j < kk; ++j) p -= Lc[kk + ldm * j] * Lc[kk + ldm * j];
@@ -326,6 +384,7 @@ __device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, bool is_f
           for (int j = i + 1; j < m; ++j) s -= Lc[j + ldm * i] * r[j];
           r[i] = s / Lc[i + ldm * i];
         }
+      }
       }
       __syncwarp();
       if (lane < m) {  // ddp.cpp:229

@@ -27,6 +27,19 @@
 namespace cgx {
 namespace rb {
 
+// Wide stores of a thread's own contiguous outputs (one node per thread: a scalar store per element touches 32
+// different sectors per warp instruction and uses 8 of their 32 bytes; ncu: 30 % of the node kernel's samples sat on
+// those stores). p must be 16-byte aligned. Host build: plain stores. 256-bit st.global.v4.f64 was tried and dropped:
+// ptxas emitted it only in the kernel without launch bounds (cuobjdump: no STG.256 in the other clones of the node
+// function, wrong Lxx on the GPU), so pairs are the widest store used here.
+CGX_HD void st2(double* p, double a, double b) {
+#if defined(__CUDA_ARCH__)
+  asm volatile("st.global.v2.f64 [%0], {%1,%2};" ::"l"(p), "d"(a), "d"(b) : "memory");
+#else
+  p[0] = a;
+  p[1] = b;
+#endif
+}
 struct V3 {
   double x, y, z;
 };
@@ -755,6 +768,7 @@ CGX_HD void arm_calcdiff_node(const ArmParams& P, bool terminal, const double* x
     }
     const double r6[6] = {fr.r.lin.x, fr.r.lin.y, fr.r.lin.z, fr.r.ang.x, fr.r.ang.y, fr.r.ang.z};
     const double wgp = P.w_gp(), wx = P.w_x(), wu = P.w_u();
+    double q2[2];  // n * n = 4 NV^2 elements, written as 16-byte pairs in flat (column-major) order
 #pragma unroll
     for (int j = 0; j < n; ++j) {
       double lx = 0.;
@@ -776,7 +790,9 @@ CGX_HD void arm_calcdiff_node(const ArmParams& P, bool terminal, const double* x
           lxx += wgp * s;
         }
         if (i == j) lxx += wx * 1.;
-        Lxx[i + n * j] = sc * lxx;
+        const int e = i + n * j;
+        q2[e & 1] = sc * lxx;
+        if ((e & 1) == 1) st2(Lxx + (e - 1), q2[0], q2[1]);
       }
     }
 #pragma unroll
@@ -804,12 +820,16 @@ CGX_HD void arm_calcdiff_node(const ArmParams& P, bool terminal, const double* x
     spd_inverse<NV>(M, Minv);
   }
 #pragma unroll
-  for (int j = 0; j < NV; ++j)
+  for (int j = 0; j < NV; ++j) {  // column j of Fu = [dt^2 Minv(:,j); dt Minv(:,j)], 16-byte stores
+    double col[n];
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
-      Fu[i + n * j] = Minv[i + NV * j] * dt2;
-      Fu[NV + i + n * j] = Minv[i + NV * j] * dt;
+      col[i] = Minv[i + NV * j] * dt2;
+      col[NV + i] = Minv[i + NV * j] * dt;
     }
+#pragma unroll
+    for (int i = 0; i < n; i += 2) st2(Fu + n * j + i, col[i], col[i + 1]);
+  }
   Dyn<NV> d;
   {
     double tau[NV];
@@ -818,6 +838,7 @@ CGX_HD void arm_calcdiff_node(const ArmParams& P, bool terminal, const double* x
   for (int kc = 0; kc < NV; ++kc) {
     double tq[NV], tv[NV];
     rnea_derivative_column<NV>(P, k, d, x + NV, kc, tq, tv);
+    double cq[n], cv[n];  // columns kc and NV + kc of Fx
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       double s1 = 0., s2 = 0.;
@@ -833,10 +854,15 @@ CGX_HD void arm_calcdiff_node(const ArmParams& P, bool terminal, const double* x
         f00 += 1.;
         f11 += 1.;
       }
-      Fx[i + n * kc] = f00;
-      Fx[i + n * (NV + kc)] = f01;
-      Fx[NV + i + n * kc] = dq * dt;
-      Fx[NV + i + n * (NV + kc)] = f11;
+      cq[i] = f00;
+      cv[i] = f01;
+      cq[NV + i] = dq * dt;
+      cv[NV + i] = f11;
+    }
+#pragma unroll
+    for (int i = 0; i < n; i += 2) {
+      st2(Fx + n * kc + i, cq[i], cq[i + 1]);
+      st2(Fx + n * (NV + kc) + i, cv[i], cv[i + 1]);
     }
   }
 }

@@ -60,7 +60,53 @@ def run(sizes=(12, 36, 72), B=4096, T=100, reps=3, peak_tflops=None):
     return out
 
 
+def run_c1(trials=2000, cpu_trials=1000):
+    """BASELINE config C1 = benchmark/lqr-optctrl.cpp:16-54: ONE OCP, ActionModelLQR(37, 12) defaults, T = 100, x0 = 0,
+    xs = {x0} x 101, us = {0} x 100, SolverDDP::solve(xs, us, MAXITER = 1), timed per call like the reference prints it
+    (mean (min-max) in ms over the trials; the reference uses 5000). GPU: through the reference-facing solve with host
+    buffers (H2D + one-CTA kernel + D2H; a single OCP is a latency measurement, the batch is the product). CPU: the
+    oracle port on one thread (the reference binary cannot be built on this box)."""
+    import time
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests"))
+    import crocoddyl_b200 as cb
+    import oracle_lib as ol
+
+    n, m, T = 37, 12, 100
+    x0 = np.zeros((1, n))
+    xs, us = np.zeros((1, T + 1, n)), np.zeros((1, T, m))
+    mod = cb.ActionModelLQR(n, m, True)
+    problem = cb.ShootingProblem(x0, [mod] * T, mod)
+    solver = cb.SolverDDP(problem)
+
+    def stats(v):
+        v = np.asarray(v)
+        return {"mean_ms": float(v.mean()), "min_ms": float(v.min()), "max_ms": float(v.max()), "trials": int(v.size)}
+
+    for _ in range(20):
+        solver.solve(xs, us, 1)
+    call, kern = [], []
+    for _ in range(trials):
+        t0 = time.perf_counter()
+        solver.solve(xs, us, 1)
+        call.append(1e3 * (time.perf_counter() - t0))
+        kern.append(solver.timing()["kernel_ms"])
+    ob = ol.OracleBatch("lqr", "ddp", T, n, m, ol.lqr_params(n, m, True), x0, fast=True)
+    cpu = []
+    for _ in range(20):
+        ob.solve(xs, us, 1, False, 1e-9, 1)
+    for _ in range(cpu_trials):
+        ob.solve(xs, us, 1, False, 1e-9, 1)
+        cpu.append(1e3 * ob.seconds)
+    np.testing.assert_allclose(solver.get("xs")[0], ob.get_all("xs")[0], rtol=1e-9, atol=1e-9)
+    return {"config": "C1: SolverDDP::solve(xs, us, 1) on ActionModelLQR(37,12), T=100, single OCP "
+                      "(benchmark/lqr-optctrl.cpp)", "gpu_call": stats(call), "gpu_kernel": stats(kern),
+            "cpu_oracle_1thread": dict(stats(cpu), kind="port")}
+
+
 if __name__ == "__main__":
+    if "--c1" in sys.argv:
+        print(json.dumps(run_c1()))
+        sys.exit(0)
     # bench_riccati.py [n ...] [--B batch] [--T horizon]: development knobs for profiling one size on a small batch
     argv = sys.argv[1:]
     kw = {}

@@ -260,6 +260,20 @@ class SolverDDP(object):
         conv = conv.astype(bool)
         return bool(conv[0]) if self.problem.B == 1 else conv
 
+    def solveFetch(self, init_xs, init_us, maxiter=100, isFeasible=False, regInit=1e-9):
+        """solve() + the xs / us getters as one call (cgx_solver_solve_fetch): returns (converged, xs, us). On the
+        thread-per-problem backend the host<->device copies of one slice of the batch overlap the solve of the others."""
+        xs, us = self._traj(init_xs, init_us)
+        p = self.problem
+        conv = np.zeros(p.B, dtype=np.uint8)
+        xs_out, us_out = np.empty_like(xs), np.empty_like(us)
+        reg = float("nan") if regInit is None else float(regInit)
+        if self._callbacks:
+            self._install_callbacks(maxiter)
+        check(lib().cgx_solver_solve_fetch(self._h, dptr(xs), dptr(us), int(maxiter), int(bool(isFeasible)), reg,
+                                           conv.ctypes.data_as(_lib._up), dptr(xs_out), dptr(us_out)))
+        return conv.astype(bool), xs_out, us_out
+
     def setCandidate(self, xs_warm=None, us_warm=None, isFeasible=False):
         xs, us = self._traj(xs_warm, us_warm)
         check(lib().cgx_solver_set_candidate(self._h, dptr(xs), dptr(us), int(bool(isFeasible))))

@@ -52,6 +52,7 @@ SIGNATURES = {
     "cgx_solver_set_storage": (C.c_int, [_vp, C.c_int]),
     "cgx_solver_enable_trace": (C.c_int, [_vp, C.c_int, C.c_int]),
     "cgx_solver_solve": (C.c_int, [_vp, _dp, _dp, C.c_int, C.c_int, C.c_double, _up]),
+    "cgx_solver_solve_fetch": (C.c_int, [_vp, _dp, _dp, C.c_int, C.c_int, C.c_double, _up, _dp, _dp]),
     "cgx_solver_upload": (C.c_int, [_vp, _dp, _dp]),
     "cgx_solver_solve_resident": (C.c_int, [_vp, C.c_int, C.c_int, C.c_double]),
     "cgx_solver_download": (C.c_int, [_vp, _up]),

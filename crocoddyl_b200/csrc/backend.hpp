@@ -75,6 +75,12 @@ struct Backend {
   // candidate from device staging buffers in user layout (null = zeros), solver-base.cpp:42-67
   virtual void set_candidate(const double* d_xs, const double* d_us, int is_feasible) = 0;
   virtual void solve(int maxiter, int is_feasible, double reginit) = 0;
+  // Optional: the same solve with the candidate read from HOST buffers and xs/us (may be null) written back to HOST
+  // buffers, in slices of the batch on separate streams so that the PCIe copies overlap the solve (thread-per-problem
+  // backend). d_xs/d_us = device staging buffers in user layout. false = not available, nothing was done.
+  virtual bool solve_pipelined(const double*, const double*, double*, double*, int, int, double, double*, double*) {
+    return false;
+  }
   virtual void compute_direction(int recalc) = 0;
   virtual void try_step(double alpha) = 0;
   // accessors: export problems [b0, b0+nb) of a field to d_out ([nb][nt][size], user layout)

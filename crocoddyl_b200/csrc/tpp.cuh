@@ -648,9 +648,11 @@ __device__ inline bool accept_step(const SolverOpts& o, bool fddp, bool is_feasi
 // alive (ncu, profiles/README.md: 19 % of the warp slots active at B = 65,536).
 template <class M>
 __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, int is_feasible0, double reginit, int chunk,
-                                 int first, const int* __restrict__ list, const int* __restrict__ nactive) {
-  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= (list ? *nactive : c.B)) return;
+                                 int first, const int* __restrict__ list, const int* __restrict__ nactive, int b_lo,
+                                 int b_hi) {
+  // a launch owns the problems [b_lo, b_hi) (slices of the batch on different streams, TppBackend::solve_pipelined)
+  const int gid = b_lo + blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (list ? *nactive : b_hi)) return;
   const int b = list ? list[gid] : gid;
   const int Bp = c.Bp;
   const bool fddp = c.fddp != 0;

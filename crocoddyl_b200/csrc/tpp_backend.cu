@@ -36,6 +36,11 @@ struct TppBackend : Backend {
     for (void* q : allocs) cudaFree(q);
     for (int i = 0; i < 4; ++i)
       if (ev[i]) cudaEventDestroy(ev[i]);
+    for (int k = 0; k < PIPE_MAX; ++k) {
+      if (pev[k]) cudaEventDestroy(pev[k]);
+      if (pstream[k]) cudaStreamDestroy(pstream[k]);
+    }
+    if (ev_reset) cudaEventDestroy(ev_reset);
     if (stream) cudaStreamDestroy(stream);
   }
   double* alloc(size_t n) {
@@ -56,9 +61,9 @@ struct TppBackend : Backend {
   }
   typedef TppLayout<M> L;
   void gather(double* d_user, const TppFieldMap& fm, double* b0p, double* b1p, const int* sel, int flip, int b0,
-              int nb, int to_rec) {
-    tpp_gather_kernel<<<dim3((nb + 63) / 64, fm.nt), 64, 0, stream>>>(d_user, b0p, b1p, sel, flip, fm, c.Bp, b0, nb,
-                                                                       to_rec);
+              int nb, int to_rec, cudaStream_t st = nullptr) {
+    tpp_gather_kernel<<<dim3((nb + 63) / 64, fm.nt), 64, 0, st ? st : stream>>>(d_user, b0p, b1p, sel, flip, fm, c.Bp,
+                                                                                 b0, nb, to_rec);
     ++last_launches;
   }
   int nblocks() const { return (c.B + 63) / 64; }
@@ -124,12 +129,79 @@ struct TppBackend : Backend {
     const char* e = getenv("CROCODDYL_B200_TPP_CHUNK");
     return e ? atoi(e) : 0;
   }
+  // solve() of a batch that arrives in HOST buffers and whose xs/us go back to HOST buffers: the batch is cut into K
+  // slices, each with its own stream: H2D copy of the slice -> layout conversion -> the whole solve loop of the slice
+  // -> conversion back -> D2H copy. The PCIe copies of one slice overlap the solve of the others (all slices are
+  // co-resident: 65,536 OCPs are one wave), the arithmetic per OCP is the same kernel as solve().
+  // CROCODDYL_B200_TPP_PIPELINE=<K> (default 4; 0/1 = off, the caller then uses upload / solve / get_all in sequence).
+  static constexpr int PIPE_MAX = 8;
+  cudaStream_t pstream[PIPE_MAX] = {};
+  cudaEvent_t pev[PIPE_MAX] = {};
+  cudaEvent_t ev_reset = nullptr;
+  double* d_out_xs = nullptr;
+  double* d_out_us = nullptr;
+  int pipeline_chunks() const {
+    const char* e = getenv("CROCODDYL_B200_TPP_PIPELINE");
+    const int k = e ? atoi(e) : 4;
+    return k > PIPE_MAX ? PIPE_MAX : k;
+  }
+  bool solve_pipelined(const double* h_xs, const double* h_us, double* d_xs, double* d_us, int maxiter,
+                       int is_feasible, double reginit, double* h_xs_out, double* h_us_out) override {
+    const int K = pipeline_chunks();
+    if (K < 2 || c.B < 1024 * K || chunk_iters() > 0 || !h_xs || !h_us) return false;
+    c.o = o;
+    const size_t T = c.T;
+    if (!ev_reset) CGX_CUDA(cudaEventCreateWithFlags(&ev_reset, cudaEventDisableTiming));
+    for (int k = 0; k < K; ++k)
+      if (!pstream[k]) {
+        CGX_CUDA(cudaStreamCreateWithFlags(&pstream[k], cudaStreamNonBlocking));
+        CGX_CUDA(cudaEventCreateWithFlags(&pev[k], cudaEventDisableTiming));
+      }
+    if (h_xs_out && !d_out_xs) d_out_xs = alloc((size_t)c.B * (T + 1) * N);
+    if (h_us_out && !d_out_us) d_out_us = alloc((size_t)c.B * T * U);
+    tpp_reset_kernel<<<(c.Bp + 63) / 64, 64, 0, stream>>>(c, is_feasible);
+    ++last_launches;
+    CGX_CUDA(cudaEventRecord(ev_reset, stream));
+    CGX_CUDA(cudaEventRecord(ev[1], stream));
+    const int per = ((c.B + K - 1) / K + 63) / 64 * 64;
+    const Fld fx = fld("xs"), fu = fld("us");
+    for (int k = 0; k < K; ++k) {
+      const int b0 = k * per;
+      if (b0 >= c.B) break;
+      const int nb = c.B - b0 < per ? c.B - b0 : per;
+      cudaStream_t st = pstream[k];
+      const size_t ox = (size_t)b0 * (T + 1) * N, nx = (size_t)nb * (T + 1) * N * sizeof(double);
+      const size_t ou = (size_t)b0 * T * U, nu = (size_t)nb * T * U * sizeof(double);
+      CGX_CUDA(cudaStreamWaitEvent(st, ev_reset, 0));
+      CGX_CUDA(cudaMemcpyAsync(d_xs + ox, h_xs + ox, nx, cudaMemcpyHostToDevice, st));
+      CGX_CUDA(cudaMemcpyAsync(d_us + ou, h_us + ou, nu, cudaMemcpyHostToDevice, st));
+      gather(d_xs + ox, fx.fm, c.xu[0], c.xu[0], nullptr, 0, b0, nb, 1, st);
+      gather(d_us + ou, fu.fm, c.xu[0], c.xu[0], nullptr, 0, b0, nb, 1, st);
+      tpp_solve_kernel<M><<<(nb + 63) / 64, TPP_BLOCK, 0, st>>>(c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr,
+                                                               b0, b0 + nb);
+      ++last_launches;
+      if (h_xs_out) {
+        gather(d_out_xs + ox, fx.fm, fx.a, fx.b, fx.sel, fx.flip, b0, nb, 0, st);
+        CGX_CUDA(cudaMemcpyAsync(h_xs_out + ox, d_out_xs + ox, nx, cudaMemcpyDeviceToHost, st));
+      }
+      if (h_us_out) {
+        gather(d_out_us + ou, fu.fm, fu.a, fu.b, fu.sel, fu.flip, b0, nb, 0, st);
+        CGX_CUDA(cudaMemcpyAsync(h_us_out + ou, d_out_us + ou, nu, cudaMemcpyDeviceToHost, st));
+      }
+      CGX_CUDA(cudaEventRecord(pev[k], st));
+      CGX_CUDA(cudaStreamWaitEvent(stream, pev[k], 0));
+    }
+    CGX_CUDA(cudaEventRecord(ev[2], stream));
+    CGX_CUDA(cudaGetLastError());
+    return true;
+  }
+
   void solve(int maxiter, int is_feasible, double reginit) override {
     c.o = o;
     const int chunk = chunk_iters();
     CGX_CUDA(cudaEventRecord(ev[1], stream));
     if (chunk <= 0 || maxiter <= chunk) {
-      tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr);
+      tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr, 0, c.B);
       ++last_launches;
     } else {
       const int cblocks = (c.B + 1023) / 1024;
@@ -140,12 +212,12 @@ struct TppBackend : Backend {
       int* d_counts = d_list + c.Bp;
       int* d_nactive = d_counts + cblocks;
       const int* fin = c.iscal + (size_t)I_FINISHED * c.Bp;
-      tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit, chunk, 1, nullptr, nullptr);
+      tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit, chunk, 1, nullptr, nullptr, 0, c.B);
       ++last_launches;
       for (int done = chunk; done < maxiter; done += chunk) {
         tpp_compact_count_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts);
         tpp_compact_scatter_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts, d_list, d_nactive);
-        tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit, chunk, 0, d_list, d_nactive);
+        tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit, chunk, 0, d_list, d_nactive, 0, c.B);
         last_launches += 3;
       }
     }

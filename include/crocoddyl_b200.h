@@ -132,6 +132,13 @@ CGX_API int cgx_solver_enable_trace(cgx_solver_t s, int on, int max_records);
  * Host buffers; the call uploads, solves on the device and downloads the per-problem scalars. */
 CGX_API int cgx_solver_solve(cgx_solver_t s, const double* init_xs, const double* init_us, int maxiter, int is_feasible,
                      double reginit, unsigned char* converged);
+/* solve() followed by get_xs() / get_us() (solver-base.hpp:162-167) as ONE call: xs_out = [B][T+1][nx] and
+ * us_out = [B][T][nu] (each may be NULL) receive the solver's xs / us after the solve. Same results as
+ * cgx_solver_solve + cgx_solver_get_all; on the thread-per-problem backend the batch is processed in slices on
+ * separate streams so that the host<->device copies of one slice overlap the solve of the others. */
+CGX_API int cgx_solver_solve_fetch(cgx_solver_t s, const double* init_xs, const double* init_us, int maxiter,
+                                   int is_feasible, double reginit, unsigned char* converged, double* xs_out,
+                                   double* us_out);
 /* The same solve split at the PCIe boundary (for pipelines that keep data resident in HBM):
  *   upload:          copies init_xs/init_us (host) into device staging buffers
  *   solve_resident:  setCandidate from the staging buffers + the whole solve loop, no host<->device copies;

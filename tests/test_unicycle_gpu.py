@@ -190,6 +190,56 @@ def test_callbacks_replay_iterations():
     np.testing.assert_allclose([r["cost"] for r in r0], to[:, 1], rtol=1e-9)
 
 
+@pytest.mark.parametrize("kind", ["ddp", "fddp"])
+def test_sliced_host_pipeline_equals_sequential_solve(kind, monkeypatch):
+    """cgx_solver_solve_fetch on the thread-per-problem backend cuts the batch into slices on separate streams (copies of
+    one slice overlap the solve of the others). Every slice runs the same kernel, so the results must be BIT-identical
+    to upload -> solve -> get_all in sequence, for ragged slice sizes too, and equal the oracle on a sample."""
+    B, T = 3 * 1024 + 37, 15  # >= 1024 problems per slice, else the call falls back to the sequence
+    x0, problem, solver, ob = _pair(kind, B, T, 77)
+    xs = np.repeat(x0[:, None, :], T + 1, 1)
+    us = np.zeros((B, T, 2))
+    monkeypatch.setenv("CROCODDYL_B200_TPP_PIPELINE", "0")
+    conv0 = solver.solve(xs, us, 30, False, 1e-9)
+    xs0, us0, sc0 = solver.xs.copy(), solver.us.copy(), solver.scalars()
+    K0, Vxx0 = solver.get("K").copy(), solver.get("Vxx").copy()
+    for slices in ("2", "3"):
+        monkeypatch.setenv("CROCODDYL_B200_TPP_PIPELINE", slices)
+        conv1, xs1, us1 = solver.solveFetch(xs, us, 30, False, 1e-9)
+        assert solver.timing()["launches"] >= 3 * int(slices)  # the sliced path ran (3+ launches per slice)
+        assert np.array_equal(conv0, conv1)
+        assert np.array_equal(xs0, xs1) and np.array_equal(us0, us1)
+        assert np.array_equal(xs0, solver.xs) and np.array_equal(us0, solver.us)
+        assert np.array_equal(K0, solver.get("K")) and np.array_equal(Vxx0, solver.get("Vxx"))
+        sc1 = solver.scalars()
+        for k in ("cost", "n_records", "converged", "stop"):
+            assert np.array_equal(sc0[k], sc1[k]), k
+        # the plain solve() entry takes the sliced path too (H2D side only)
+        conv2 = solver.solve(xs, us, 30, False, 1e-9)
+        assert np.array_equal(conv0, conv2) and np.array_equal(xs0, solver.xs)
+    nb = 64
+    ob2 = ol.OracleBatch("unicycle", kind, T, 3, 2, ol.unicycle_params(), x0[-nb:])
+    ob2.solve(xs[-nb:], us[-nb:], 30, False, 1e-9)
+    assert np.array_equal(ob2.scalars()["n_records"], sc0["n_records"][-nb:])
+    np.testing.assert_allclose(xs0[-nb:], ob2.get_all("xs"), **TOL)
+    np.testing.assert_allclose(us0[-nb:], ob2.get_all("us"), **TOL)
+
+
+def test_solve_fetch_on_the_cta_backend_falls_back_to_sequence():
+    """Arm / LQR (CTA-per-problem backend) have no sliced pipeline: solve_fetch = solve + get_all."""
+    n, m, T, B = 6, 2, 5, 3
+    mod = cb.ActionModelLQR(n, m, False)
+    rng = np.random.default_rng(0)
+    x0 = rng.standard_normal((B, n))
+    problem = cb.ShootingProblem(x0, [mod] * T, mod)
+    solver = cb.SolverDDP(problem)
+    xs, us = np.repeat(x0[:, None, :], T + 1, 1), np.zeros((B, T, m))
+    conv, xs1, us1 = solver.solveFetch(xs, us, 10)
+    assert np.array_equal(xs1, solver.xs) and np.array_equal(us1, solver.us)
+    conv0 = solver.solve(xs, us, 10)
+    assert np.array_equal(conv, conv0) and np.array_equal(xs1, solver.xs)
+
+
 def test_full_size_batch_sampled_against_oracle():
     """BASELINE config C2: B = 65,536, T = 100. The oracle checks a 2,048-problem sample; the rest is covered by
     size-independent properties (converged => feasible, gaps closed, stop < th_stop, cost decreased)."""

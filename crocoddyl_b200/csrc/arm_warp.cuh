@@ -92,13 +92,7 @@ __device__ void arm_calc_warp(const double* params, bool terminal, const double*
     W.c[lane][3] = ci.ang.x; W.c[lane][4] = ci.ang.y; W.c[lane][5] = ci.ang.z;
     W.pa0[lane][0] = p0.lin.x; W.pa0[lane][1] = p0.lin.y; W.pa0[lane][2] = p0.lin.z;
     W.pa0[lane][3] = p0.ang.x; W.pa0[lane][4] = p0.ang.y; W.pa0[lane][5] = p0.ang.z;
-  }
-  __syncwarp();
-  // S3: articulated-inertia sweep on lanes 0..5 (lane r = row r). Lane NV's frame placement / log6 / cost chain is the
-  // other side of the same branch: it needs only W.X, so the scheduler can interleave it with the sweep (the sweep
-  // yields at every __syncwarp(M6)) instead of the warp waiting for it before the sweep starts.
-  constexpr unsigned M6 = 0x3fu;
-  if (lane == (NV >= 6 ? NV : 31)) {
+  } else if (lane == NV) {
     const int fp = P.frame_parent();
     SE3 oM = ld_se3(W.X[0]);
 #pragma unroll
@@ -108,7 +102,11 @@ __device__ void arm_calc_warp(const double* params, bool terminal, const double*
     fr.rMf = actInv(P.Mref(), compose(oM, P.frame_placement()));
     fr.r = log6(fr.rMf, fr.theta, fr.w);
     W.cost = diff_cost<NV>(P, fr, x, u);
-  } else if (lane < 6) {
+  }
+  __syncwarp();
+  // S3: articulated-inertia sweep on lanes 0..5 (lane r = row r); the other lanes skip it
+  constexpr unsigned M6 = 0x3fu;
+  if (lane < 6) {
     const int r = lane;
     double Ir[6] = {0., 0., 0., 0., 0., 0.};  // row r of the inertia propagated from the child
     double par = 0.;                          // component r of the propagated bias force
@@ -184,7 +182,7 @@ __device__ void arm_calc_warp(const double* params, bool terminal, const double*
       }
     }
   }
-  if (lane == (NV >= 6 ? NV : 31)) *cost_out = (dt != 0.) ? dt * W.cost : W.cost;
+  if (lane == NV) *cost_out = (dt != 0.) ? dt * W.cost : W.cost;
 }
 
 }  // namespace cgx

@@ -165,6 +165,20 @@ class SolverDDP {
                            is_feasible ? 1 : 0, regInit, converged_.data()));
     return converged_[0] != 0;
   }
+  // solve(...) followed by get_xs() / get_us() as one call (cgx_solver_solve_fetch): xs_out = [B][T+1][nx],
+  // us_out = [B][T][nu] are resized and filled; on the unicycle backend the copies overlap the solve.
+  bool solve(const std::vector<double>& init_xs, const std::vector<double>& init_us, std::vector<double>& xs_out,
+             std::vector<double>& us_out, std::size_t maxiter = 100, bool is_feasible = false, double regInit = 1e-9) {
+    const std::size_t B = problem_->get_batch(), T = problem_->get_T(), nx = problem_->get_nx(), nu = problem_->get_nu_max();
+    if (init_xs.size() != B * (T + 1) * nx || init_us.size() != B * T * nu)
+      throw Exception(CGX_ERR_INVALID, "Warm start has wrong dimension");
+    xs_out.resize(B * (T + 1) * nx);
+    us_out.resize(B * T * nu);
+    converged_.assign(B, 0);
+    check(cgx_solver_solve_fetch(h_, init_xs.data(), init_us.data(), (int)maxiter, is_feasible ? 1 : 0, regInit,
+                                 converged_.data(), xs_out.data(), us_out.data()));
+    return converged_[0] != 0;
+  }
   const std::vector<unsigned char>& converged() const { return converged_; }
   void setCandidate(const std::vector<double>& xs, const std::vector<double>& us, bool is_feasible = false) {
     check(cgx_solver_set_candidate(h_, xs.empty() ? nullptr : xs.data(), us.empty() ? nullptr : us.data(), is_feasible ? 1 : 0));

@@ -35,6 +35,15 @@ int main(int argc, char** argv) {
     printf("\nK0");
     for (double v : K0) printf(" %.17g", v);
     printf("\n");
+    // the fused solve + getters overload must hand back exactly what the getters hold
+    {
+      std::vector<double> xf, uf;
+      const bool ok2 = ddp.solve(xs, us, xf, uf, 100, false, 1e-9);
+      if (ok2 != ok || xf != xo || uf != uo || xf != ddp.get_xs()) {
+        printf("solve_fetch mismatch\n");
+        return 6;
+      }
+    }
     // argument checking mirrors the reference's throw_pretty messages
     try {
       ddp.solve(std::vector<double>(3, 0.), us);

@@ -180,6 +180,16 @@ struct TppBackend : Backend {
       tpp_solve_kernel<M><<<(nb + 63) / 64, TPP_BLOCK, 0, st>>>(c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr,
                                                                b0, b0 + nb);
       ++last_launches;
+    }
+    // second pass in issue order: the copies back are enqueued after EVERY slice's upload and solve, so that no
+    // upload can queue up behind a download that waits for a solve
+    for (int k = 0; k < K; ++k) {
+      const int b0 = k * per;
+      if (b0 >= c.B) break;
+      const int nb = c.B - b0 < per ? c.B - b0 : per;
+      cudaStream_t st = pstream[k];
+      const size_t ox = (size_t)b0 * (T + 1) * N, nx = (size_t)nb * (T + 1) * N * sizeof(double);
+      const size_t ou = (size_t)b0 * T * U, nu = (size_t)nb * T * U * sizeof(double);
       if (h_xs_out) {
         gather(d_out_xs + ox, fx.fm, fx.a, fx.b, fx.sel, fx.flip, b0, nb, 0, st);
         CGX_CUDA(cudaMemcpyAsync(h_xs_out + ox, d_out_xs + ox, nx, cudaMemcpyDeviceToHost, st));

@@ -59,3 +59,13 @@ def test_lqr_param_packing_is_column_major():
     p = m.params()
     assert p.shape == (1 + 9 + 6 + 3 + 9 + 6 + 4 + 3 + 2,)
     np.testing.assert_array_equal(p[10:16], m.Fu.ravel(order="F"))
+
+
+def test_null_solver_handle_is_an_invalid_argument_not_a_crash():
+    """solve / solve_fetch on a NULL handle return CGX_ERR_INVALID with a message (no exception crosses the C ABI)."""
+    L = cb.lib()
+    conv = np.zeros(1, dtype=np.uint8)
+    up = conv.ctypes.data_as(_lib._up)
+    assert L.cgx_solver_solve(None, None, None, 1, 0, 1e-9, up) == -1
+    assert L.cgx_solver_solve_fetch(None, None, None, 1, 0, 1e-9, up, None, None) == -1
+    assert b"NULL" in L.cgx_last_error()

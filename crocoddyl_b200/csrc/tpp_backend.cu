@@ -38,6 +38,8 @@ struct TppBackend : Backend {
       if (ev[i]) cudaEventDestroy(ev[i]);
     for (int k = 0; k < PIPE_MAX; ++k) {
       if (pev[k]) cudaEventDestroy(pev[k]);
+      for (int j = 0; j < 3; ++j)
+        if (ptime[k][j]) cudaEventDestroy(ptime[k][j]);
       if (pstream[k]) cudaStreamDestroy(pstream[k]);
     }
     if (ev_reset) cudaEventDestroy(ev_reset);
@@ -138,6 +140,7 @@ struct TppBackend : Backend {
   cudaStream_t pstream[PIPE_MAX] = {};
   cudaEvent_t pev[PIPE_MAX] = {};
   cudaEvent_t ev_reset = nullptr;
+  cudaEvent_t ptime[PIPE_MAX][3] = {};  // CROCODDYL_B200_TPP_PIPELINE_TRACE=1: upload done / solve done / download done
   double* d_out_xs = nullptr;
   double* d_out_us = nullptr;
   int pipeline_chunks() const {
@@ -157,6 +160,12 @@ struct TppBackend : Backend {
         CGX_CUDA(cudaStreamCreateWithFlags(&pstream[k], cudaStreamNonBlocking));
         CGX_CUDA(cudaEventCreateWithFlags(&pev[k], cudaEventDisableTiming));
       }
+    const char* pte = getenv("CROCODDYL_B200_TPP_PIPELINE_TRACE");
+    const bool ptrace = pte && atoi(pte) != 0;
+    if (ptrace)
+      for (int k = 0; k < K; ++k)
+        for (int j = 0; j < 3; ++j)
+          if (!ptime[k][j]) CGX_CUDA(cudaEventCreate(&ptime[k][j]));
     if (h_xs_out && !d_out_xs) d_out_xs = alloc((size_t)c.B * (T + 1) * N);
     if (h_us_out && !d_out_us) d_out_us = alloc((size_t)c.B * T * U);
     tpp_reset_kernel<<<(c.Bp + 63) / 64, 64, 0, stream>>>(c, is_feasible);
@@ -177,9 +186,11 @@ struct TppBackend : Backend {
       CGX_CUDA(cudaMemcpyAsync(d_us + ou, h_us + ou, nu, cudaMemcpyHostToDevice, st));
       gather(d_xs + ox, fx.fm, c.xu[0], c.xu[0], nullptr, 0, b0, nb, 1, st);
       gather(d_us + ou, fu.fm, c.xu[0], c.xu[0], nullptr, 0, b0, nb, 1, st);
+      if (ptrace) CGX_CUDA(cudaEventRecord(ptime[k][0], st));
       tpp_solve_kernel<M><<<(nb + 63) / 64, TPP_BLOCK, 0, st>>>(c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr,
                                                                b0, b0 + nb);
       ++last_launches;
+      if (ptrace) CGX_CUDA(cudaEventRecord(ptime[k][1], st));
     }
     // second pass in issue order: the copies back are enqueued after EVERY slice's upload and solve, so that no
     // upload can queue up behind a download that waits for a solve
@@ -198,10 +209,21 @@ struct TppBackend : Backend {
         gather(d_out_us + ou, fu.fm, fu.a, fu.b, fu.sel, fu.flip, b0, nb, 0, st);
         CGX_CUDA(cudaMemcpyAsync(h_us_out + ou, d_out_us + ou, nu, cudaMemcpyDeviceToHost, st));
       }
+      if (ptrace) CGX_CUDA(cudaEventRecord(ptime[k][2], st));
       CGX_CUDA(cudaEventRecord(pev[k], st));
       CGX_CUDA(cudaStreamWaitEvent(stream, pev[k], 0));
     }
     CGX_CUDA(cudaEventRecord(ev[2], stream));
+    if (ptrace) {  // development aid: device timeline of the slices relative to the start of the call (ms)
+      CGX_CUDA(cudaStreamSynchronize(stream));
+      for (int k = 0; k < K && k * per < c.B; ++k) {
+        float a = 0, b = 0, d = 0;
+        cudaEventElapsedTime(&a, ev[1], ptime[k][0]);
+        cudaEventElapsedTime(&b, ev[1], ptime[k][1]);
+        cudaEventElapsedTime(&d, ev[1], ptime[k][2]);
+        fprintf(stderr, "[tpp pipeline] slice %d: upload done %.2f, solve done %.2f, download done %.2f ms\n", k, a, b, d);
+      }
+    }
     CGX_CUDA(cudaGetLastError());
     return true;
   }

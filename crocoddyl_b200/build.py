@@ -71,5 +71,19 @@ def build(force=False, quiet=False, variant=None, extra=None):
     return LIB
 
 
+PARITY_FLAGS = ["-fmad=false", "-DCGX_PARITY=1"]
+
+
+def build_parity(force=False, quiet=False):
+    """lib/libcrocoddyl_b200_parity.so: the same sources without FMA contraction (-fmad=false, as the oracle's
+    -ffp-contract=off) and with IEEE divisions by the LLT pivots instead of reciprocal multiplies (-DCGX_PARITY).
+    Used by the parity tests that demand the reference's exact iteration count / accept sequence on every problem
+    (select it at run time with CROCODDYL_B200_LIB); the default build is the fast one."""
+    extra = {src: globals()["EXTRA"].get(src, []) + PARITY_FLAGS for src in SOURCES}
+    return build(force=force, quiet=quiet, variant="parity", extra=extra)
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv))
+    if "--parity" in sys.argv:
+        print(build_parity(force="--force" in sys.argv))

@@ -12,6 +12,7 @@ using namespace cgx;
 struct cgx_problem_s {
   ProblemDesc d;
   Backend* pb = nullptr;  // backend instance serving the problem-level API (calc/calcDiff/rollout)
+  std::vector<Backend*> live;  // backends of the solvers created on this problem (told about set_x0)
   double* d_tmp_xs = nullptr;
   double* d_tmp_us = nullptr;
   double* d_tmp_cost = nullptr;
@@ -254,6 +255,8 @@ int cgx_problem_set_x0(cgx_problem_t p, const double* x0s) {
   p->d.h_x0.assign(x0s, x0s + (size_t)p->d.B * p->d.nx);
   CGX_CUDA(cudaMemcpy(p->d.d_x0, x0s, p->d.h_x0.size() * sizeof(double), cudaMemcpyHostToDevice));
   if (p->pb) p->pb->x0_changed();
+  // every live solver keeps (or aliases) its own view of x0: shooting.hxx:393-400 changes what the NEXT solve() sees
+  for (Backend* be : p->live) be->x0_changed();
   return CGX_OK;
   CGX_CATCH
 }
@@ -343,6 +346,7 @@ int cgx_solver_create(cgx_solver_t* out, cgx_problem_t p, int solver_kind) {
     cgx_solver_destroy(s);
     throw;
   }
+  p->live.push_back(s->be);
   *out = s;
   return CGX_OK;
   CGX_CATCH
@@ -350,6 +354,12 @@ int cgx_solver_create(cgx_solver_t* out, cgx_problem_t p, int solver_kind) {
 
 int cgx_solver_destroy(cgx_solver_t s) {
   if (!s) return CGX_OK;
+  if (s->p && s->be)
+    for (size_t i = 0; i < s->p->live.size(); ++i)
+      if (s->p->live[i] == s->be) {
+        s->p->live.erase(s->p->live.begin() + i);
+        break;
+      }
   delete s->be;
   if (s->d_init_xs) cudaFree(s->d_init_xs);
   if (s->d_init_us) cudaFree(s->d_init_us);
@@ -712,6 +722,7 @@ int cgx_solver_get_trace(cgx_solver_t s, int b, double* out, int max_records) {
   if (!s) throw InvalidArg("Invalid argument: NULL");
   if (b < 0 || b >= s->p->d.B) throw InvalidArg("Invalid argument: b out of range");
   if (!s->be->trace_on) throw InvalidArg("trace recording is not enabled (cgx_solver_enable_trace)");
+  if (out && max_records < 0) throw InvalidArg("Invalid argument: max_records is negative");
   fetch_scalars(s);
   int n = (int)s->h_scal[(size_t)b * 17 + 12];
   if (n > s->be->trace_cap) n = s->be->trace_cap;

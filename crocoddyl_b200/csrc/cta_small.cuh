@@ -321,7 +321,7 @@ __device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, bool is_f
             double sv = Lr[i * (i + 1) / 2 + kk];
 #pragma unroll
             for (int j = 0; j < kk; ++j) sv -= Lr[i * (i + 1) / 2 + j] * Lr[kk * (kk + 1) / 2 + j];
-            Lr[i * (i + 1) / 2 + kk] = sv * pinv;
+            Lr[i * (i + 1) / 2 + kk] = div_pivot(sv, p, pinv);
           }
         }
         if (notpd) {
@@ -337,14 +337,14 @@ __device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, bool is_f
             double sv = rr[i];
 #pragma unroll
             for (int j = 0; j < i; ++j) sv -= Lr[i * (i + 1) / 2 + j] * rr[j];
-            rr[i] = sv * rinv[i];
+            rr[i] = div_pivot(sv, Lr[i * (i + 1) / 2 + i], rinv[i]);
           }
 #pragma unroll
           for (int i = KM - 1; i >= 0; --i) {
             double sv = rr[i];
 #pragma unroll
             for (int j = i + 1; j < KM; ++j) sv -= Lr[j * (j + 1) / 2 + i] * rr[j];
-            rr[i] = sv * rinv[i];
+            rr[i] = div_pivot(sv, Lr[i * (i + 1) / 2 + i], rinv[i]);
           }
           double* r = (lane < n) ? (Kg + ldm * lane) : kg;
 #pragma unroll

@@ -400,7 +400,7 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
         double s = Lc[i + U * kk];
 #pragma unroll
         for (int j = 0; j < kk; ++j) s -= Lc[i + U * j] * Lc[kk + U * j];
-        Lc[i + U * kk] = s * Linv[kk];
+        Lc[i + U * kk] = div_pivot(s, p, Linv[kk]);
       }
     }
     if (fail) return 1;
@@ -420,14 +420,14 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
         double s = rr[i];
 #pragma unroll
         for (int j = 0; j < i; ++j) s -= Lc[i + U * j] * rr[j];
-        rr[i] = s * Linv[i];
+        rr[i] = div_pivot(s, Lc[i + U * i], Linv[i]);
       }
 #pragma unroll
       for (int i = U - 1; i >= 0; --i) {
         double s = rr[i];
 #pragma unroll
         for (int j = i + 1; j < U; ++j) s -= Lc[j + U * i] * rr[j];
-        rr[i] = s * Linv[i];
+        rr[i] = div_pivot(s, Lc[i + U * i], Linv[i]);
       }
 #pragma unroll
       for (int i = 0; i < U; ++i) {

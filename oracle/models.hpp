@@ -6,6 +6,7 @@
 //   ActionModelLQR      include/crocoddyl/core/actions/lqr.hxx:14-70, lqr.hpp:88-95
 //   ActionModelUnicycle include/crocoddyl/core/actions/unicycle.hxx:13-73, unicycle.hpp:78-80
 #pragma once
+#include <cstdint>
 #include <memory>
 #include <stdexcept>
 #include <string>
@@ -32,8 +33,31 @@ struct ActionData {
 struct ActionModel {
   int nx, ndx, nu, nr;
   Vec unone;
-  ActionModel(int nx_, int nu_, int nr_) : nx(nx_), ndx(nx_), nu(nu_), nr(nr_), unone(nu_, 0.) {}
+  // control limits, action-base.hxx:19-22,117-140: +-inf by default; has_control_limits = some finite entry in BOTH
+  Vec u_lb, u_ub;
+  bool has_control_limits;
+  ActionModel(int nx_, int nu_, int nr_)
+      : nx(nx_), ndx(nx_), nu(nu_), nr(nr_), unone(nu_, 0.), u_lb(nu_, -INFINITY), u_ub(nu_, INFINITY),
+        has_control_limits(false) {}
   virtual ~ActionModel() {}
+  void set_u_lb(const Vec& v) {
+    if ((int)v.size() != nu) throw std::invalid_argument("Invalid argument: lower bound has wrong dimension");
+    u_lb = v;
+    update_has_control_limits();
+  }
+  void set_u_ub(const Vec& v) {
+    if ((int)v.size() != nu) throw std::invalid_argument("Invalid argument: upper bound has wrong dimension");
+    u_ub = v;
+    update_has_control_limits();
+  }
+  void update_has_control_limits() {  // action-base.hxx:138-140
+    bool a = false, b = false;
+    for (int i = 0; i < nu; ++i) {
+      a = a || std::isfinite(u_lb[i]);
+      b = b || std::isfinite(u_ub[i]);
+    }
+    has_control_limits = a && b;
+  }
   virtual void calc(ActionData& d, const Vec& x, const Vec& u) = 0;
   virtual void calcDiff(ActionData& d, const Vec& x, const Vec& u) = 0;
   virtual std::shared_ptr<ActionData> createData() { return std::make_shared<ActionData>(nx, ndx, nu, nr); }
@@ -57,6 +81,25 @@ struct ActionModel {
       throw std::invalid_argument("Invalid argument: u has wrong dimension (it should be " + std::to_string(nu) + ")");
   }
 };
+
+// Sensitivity experiment only (liboracle_perturb.so, -DORACLE_PERTURB_SINCOS): move the result of sin / cos by one
+// ulp for about a quarter of the arguments (chosen by a hash of the argument's bits). Models two correct libm's that
+// round differently (glibc on the host vs CUDA's sin/cos on the device, both < 1-2 ulp) and measures how many solves
+// change their iteration count because of that alone (tools/sincos_sensitivity.py, profiles/r02_sincos_sensitivity.json).
+inline double libm_result(double v, double arg) {
+#ifdef ORACLE_PERTURB_SINCOS
+  uint64_t h;
+  std::memcpy(&h, &arg, 8);
+  h ^= h >> 33;
+  h *= 0xff51afd7ed558ccdULL;
+  h ^= h >> 33;
+  if ((h & 7) == 0) return std::nextafter(v, INFINITY);
+  if ((h & 7) == 1) return std::nextafter(v, -INFINITY);
+#else
+  (void)arg;
+#endif
+  return v;
+}
 
 // ---------------------------------------------------------------------------------------------
 // ActionModelLQR — lqr.hxx:14-70
@@ -123,8 +166,8 @@ struct ActionModelUnicycle : ActionModel {
   }
   void calc(ActionData& d, const Vec& x, const Vec& u) override {
     check(x, u);
-    const double c = std::cos(x[2]);
-    const double s = std::sin(x[2]);
+    const double c = libm_result(std::cos(x[2]), x[2]);
+    const double s = libm_result(std::sin(x[2]), x[2]);
     d.xnext[0] = x[0] + c * u[0] * dt;  // unicycle.hxx:38
     d.xnext[1] = x[1] + s * u[0] * dt;
     d.xnext[2] = x[2] + u[1] * dt;
@@ -142,8 +185,8 @@ struct ActionModelUnicycle : ActionModel {
     for (int i = 0; i < 2; ++i) d.Lu[i] = u[i] * w_u;  // :62
     for (int i = 0; i < 3; ++i) d.Lxx(i, i) = w_x;     // :63
     for (int i = 0; i < 2; ++i) d.Luu(i, i) = w_u;     // :64
-    const double c = std::cos(x[2]);
-    const double s = std::sin(x[2]);
+    const double c = libm_result(std::cos(x[2]), x[2]);
+    const double s = libm_result(std::sin(x[2]), x[2]);
     d.Fx(0, 2) = -s * u[0] * dt;  // :69-73
     d.Fx(1, 2) = c * u[0] * dt;
     d.Fu(0, 0) = c * dt;

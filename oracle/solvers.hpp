@@ -392,8 +392,8 @@ struct SolverDDP : SolverAbstract {
     cost_try += problem->terminal_data->cost;
     if (raiseIfNaN(cost_try)) throw SolveError("forward_error");
   }
-  // ddp.cpp:298-310
-  void computeGains(int t) {
+  // ddp.cpp:298-310 (virtual: SolverBoxDDP / SolverBoxFDDP replace it, box-ddp.cpp:46-74)
+  virtual void computeGains(int t) {
     const int nu = problem->running_models[t]->nu;
     if (nu > 0) {
       if (!Quu_llt[t].compute(Quu[t])) throw SolveError("backward_error");

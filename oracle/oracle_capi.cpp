@@ -10,6 +10,7 @@
 #include <cstring>
 #include <string>
 #include "arm.hpp"
+#include "box.hpp"
 #include "solvers.hpp"
 
 using namespace oracle;
@@ -17,7 +18,7 @@ using namespace oracle;
 namespace {
 
 enum { KIND_LQR = 0, KIND_UNICYCLE = 1, KIND_ARM = 2 };
-enum { SOLVER_DDP = 0, SOLVER_FDDP = 1 };
+enum { SOLVER_DDP = 0, SOLVER_FDDP = 1, SOLVER_BOXDDP = 2, SOLVER_BOXFDDP = 3 };
 
 struct Batch {
   int kind, solver_kind, B, T, nx, nu;
@@ -116,6 +117,10 @@ void* orc_batch_create(int kind, int solver_kind, int B, int T, int nx, int nu, 
       bt->problems.push_back(prob);
       if (solver_kind == SOLVER_FDDP)
         bt->solvers.push_back(std::make_shared<SolverFDDP>(prob));
+      else if (solver_kind == SOLVER_BOXDDP)
+        bt->solvers.push_back(std::make_shared<SolverBoxDDP>(prob));
+      else if (solver_kind == SOLVER_BOXFDDP)
+        bt->solvers.push_back(std::make_shared<SolverBoxFDDP>(prob));
       else
         bt->solvers.push_back(std::make_shared<SolverDDP>(prob));
     }
@@ -128,6 +133,51 @@ void* orc_batch_create(int kind, int solver_kind, int B, int T, int nx, int nu, 
 }
 
 void orc_batch_destroy(void* h) { delete (Batch*)h; }
+
+// ActionModelAbstract::set_u_lb / set_u_ub (action-base.hxx:117-140) on the running model(s) of every problem.
+// lb/ub: nu doubles shared by all problems (per_problem == 0) or B blocks. +-inf = unbounded.
+int orc_batch_set_u_bounds(void* h, const double* lb, const double* ub, int per_problem) {
+  Batch* bt = (Batch*)h;
+  const int nu = bt->nu;
+  for (int b = 0; b < bt->B; ++b) {
+    const double* l = lb + (per_problem ? (size_t)b * nu : 0);
+    const double* u = ub + (per_problem ? (size_t)b * nu : 0);
+    ShootingProblem& p = *bt->problems[b];
+    if (per_problem && b > 0 && p.running_models[0] == bt->problems[0]->running_models[0]) return -1;  // shared model
+    ActionModel* last = nullptr;
+    for (auto& m : p.running_models) {
+      if (m.get() == last) continue;
+      last = m.get();
+      m->set_u_lb(Vec(l, l + nu));
+      m->set_u_ub(Vec(u, u + nu));
+    }
+  }
+  return 0;
+}
+
+// BoxQP::solve (box-qp.cpp:52-186) stand-alone: H (n x n column-major), q, lb, ub, xinit -> x, Hff_inv (nf x nf
+// column-major, nf returned through *nf_out), free/clamped flags (clamped[i] = 1). Returns the number of Newton
+// iterations, or -1 on "backward_error".
+int orc_boxqp_solve(int n, const double* H, const double* q, const double* lb, const double* ub, const double* xinit,
+                    int maxiter, double th_acceptstep, double th_grad, double reg, double* x_out, double* Hff_inv_out,
+                    int* nf_out, int* clamped_out) {
+  BoxQP qp(n, maxiter, th_acceptstep, th_grad, reg);
+  Mat Hm(n, n);
+  std::memcpy(Hm.d.data(), H, sizeof(double) * n * n);
+  try {
+    const BoxQPSolution& sol = qp.solve(Hm, Vec(q, q + n), Vec(lb, lb + n), Vec(ub, ub + n), Vec(xinit, xinit + n));
+    std::memcpy(x_out, sol.x.data(), sizeof(double) * n);
+    if (Hff_inv_out) std::memcpy(Hff_inv_out, sol.Hff_inv.d.data(), sizeof(double) * sol.Hff_inv.d.size());
+    if (nf_out) *nf_out = sol.Hff_inv.r;
+    if (clamped_out) {
+      for (int i = 0; i < n; ++i) clamped_out[i] = 0;
+      for (int i : sol.clamped_idx) clamped_out[i] = 1;
+    }
+  } catch (SolveError&) {
+    return -1;
+  }
+  return qp.iters;
+}
 
 // thresholds: name in {th_acceptstep, th_stop, th_grad, th_stepdec, th_stepinc, th_acceptnegstep, regfactor, regmin, regmax}
 int orc_batch_set(void* h, const char* name, double v) {

@@ -11,7 +11,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 KIND = {"lqr": 0, "unicycle": 1, "arm": 2}
-SOLVER = {"ddp": 0, "fddp": 1}
+SOLVER = {"ddp": 0, "fddp": 1, "boxddp": 2, "boxfddp": 3}
 SCALARS = ["cost", "stop", "d0", "d1", "xreg", "ureg", "steplength", "dV", "dVexp", "iter", "is_feasible",
            "converged", "n_records", "cost_try", "was_feasible", "_"]
 TRACE = ["iter", "cost", "stop", "d0", "d1", "xreg", "ureg", "steplength", "is_feasible", "dV", "dVexp",
@@ -46,6 +46,9 @@ def load(fast=False):
     lib.orc_kkt_solve.argtypes = [C.c_void_p, C.c_int, _dp, _dp, C.c_int, _dp, _dp]
     lib.orc_numdiff.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, _dp, _dp, _dp]
     lib.orc_arm_op.argtypes = [_dp, C.c_long, C.c_char_p, _dp, _dp]
+    lib.orc_batch_set_u_bounds.argtypes = [C.c_void_p, _dp, _dp, C.c_int]
+    lib.orc_boxqp_solve.argtypes = [C.c_int, _dp, _dp, _dp, _dp, _dp, C.c_int, C.c_double, C.c_double, C.c_double, _dp,
+                                    _dp, _ip, _ip]
     return lib
 
 
@@ -76,6 +79,12 @@ class OracleBatch:
     def set_alphas(self, alphas):
         a = np.ascontiguousarray(alphas, dtype=np.float64)
         assert self.lib.orc_batch_set_alphas(self.h, _p(a), a.size) == 0
+
+    def set_u_bounds(self, lb, ub):
+        """ActionModelAbstract::set_u_lb / set_u_ub on the running model: [nu] shared, or [B, nu] (per-problem models)."""
+        lb = np.ascontiguousarray(lb, dtype=np.float64)
+        ub = np.ascontiguousarray(ub, dtype=np.float64)
+        assert self.lib.orc_batch_set_u_bounds(self.h, _p(lb), _p(ub), int(lb.ndim == 2)) == 0
 
     def solve(self, init_xs=None, init_us=None, maxiter=100, is_feasible=False, reginit=1e-9, nthreads=0):
         xs = None if init_xs is None else np.ascontiguousarray(init_xs, dtype=np.float64)
@@ -176,6 +185,23 @@ class OracleBatch:
                     "Lx": v[n * n + n * m:n * n + n * m + n], "Lu": v[n * n + n * m + n:]}
 
         return split(a), split(d)
+
+
+def boxqp_solve(H, q, lb, ub, xinit, maxiter=100, th_acceptstep=0.1, th_grad=1e-9, reg=1e-9):
+    """BoxQP(nx, maxiter, th_acceptstep, th_grad, reg).solve(H, q, lb, ub, xinit) of the oracle (box-qp.cpp:52-186).
+    -> dict(x, Hff_inv, clamped (bool mask), iters); raises ArithmeticError on "backward_error"."""
+    lib = load(False)
+    n = len(q)
+    f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+    Hc = np.ascontiguousarray(np.asarray(H, dtype=np.float64).T)  # column-major
+    x, Hi = np.zeros(n), np.zeros(n * n)
+    nf, cl = C.c_int(0), np.zeros(n, dtype=np.int32)
+    it = lib.orc_boxqp_solve(n, _p(Hc), _p(f(q)), _p(f(lb)), _p(f(ub)), _p(f(xinit)), maxiter, th_acceptstep, th_grad,
+                             reg, _p(x), _p(Hi), C.byref(nf), cl.ctypes.data_as(_ip))
+    if it < 0:
+        raise ArithmeticError("backward_error")
+    k = nf.value
+    return dict(x=x, Hff_inv=Hi[:k * k].reshape(k, k, order="F"), clamped=cl.astype(bool), iters=it)
 
 
 def lqr_params(n, m, drift_free=True, Fx=None, Fu=None, f0=None, Lxx=None, Lxu=None, Luu=None, lx=None, lu=None):

@@ -80,20 +80,42 @@ def test_box_qp_optimum_matches_scipy(seed):
     assert np.all((sol["x"][sol["clamped"]] == lb[sol["clamped"]]) | (sol["x"][sol["clamped"]] == ub[sol["clamped"]]))
 
 
-def _lqr_case(seed, n=4, m=3, T=12, B=3):
+def _lqr_case(seed, n=4, m=2, T=15, B=3, fu=0.3):
+    """-> params [B, np], x0 [B, n], n, m, T, B, list of the model matrices (for the independent NumPy cost below)."""
     rng = np.random.default_rng(seed)
-    P = []
+    P, M = [], []
     for b in range(B):
         A, Bm = rng.standard_normal((n, n)), rng.standard_normal((m, m))
-        P.append(ol.lqr_params(n, m, False, Fx=np.eye(n) + 0.1 * rng.standard_normal((n, n)), Fu=rng.standard_normal((n, m)),
-                               f0=0.1 * rng.standard_normal(n), Lxx=A.T @ A / n + np.eye(n), Lxu=0.1 * rng.standard_normal((n, m)),
-                               Luu=Bm.T @ Bm / m + 0.1 * np.eye(m), lx=rng.standard_normal(n), lu=rng.standard_normal(m)))
-    return np.stack(P), rng.standard_normal((B, n)), n, m, T, B
+        d = dict(Fx=np.eye(n) + 0.05 * rng.standard_normal((n, n)), Fu=fu * rng.standard_normal((n, m)),
+                 f0=0.02 * rng.standard_normal(n), Lxx=A.T @ A / n + np.eye(n), Lxu=0.05 * rng.standard_normal((n, m)),
+                 Luu=Bm.T @ Bm / m + 0.5 * np.eye(m), lx=0.1 * rng.standard_normal(n), lu=0.1 * rng.standard_normal(m))
+        M.append(d)
+        P.append(ol.lqr_params(n, m, False, **d))
+    return np.stack(P), rng.standard_normal((B, n)), n, m, T, B, M
+
+
+def _cost_and_gradient(uflat, d, x0, T, m):
+    """Total cost of the rollout of us on an LQR problem and its gradient by the adjoint recursion — plain NumPy,
+    independent of the oracle (the objective handed to scipy)."""
+    U = uflat.reshape(T, m)
+    x, c, xs = x0, 0., [x0]
+    for t in range(T):
+        u = U[t]
+        c += 0.5 * x @ d["Lxx"] @ x + 0.5 * u @ d["Luu"] @ u + x @ d["Lxu"] @ u + d["lx"] @ x + d["lu"] @ u
+        x = d["Fx"] @ x + d["Fu"] @ u + d["f0"]
+        xs.append(x)
+    c += 0.5 * x @ d["Lxx"] @ x + d["lx"] @ x
+    lam, g = d["Lxx"] @ x + d["lx"], np.zeros((T, m))
+    for t in range(T - 1, -1, -1):
+        x, u = xs[t], U[t]
+        g[t] = d["Luu"] @ u + d["Lxu"].T @ x + d["lu"] + d["Fu"].T @ lam
+        lam = d["Lxx"] @ x + d["Lxu"] @ u + d["lx"] + d["Fx"].T @ lam
+    return c, g.ravel()
 
 
 @pytest.mark.parametrize("kind", ["boxddp", "boxfddp"])
 def test_box_solvers_without_limits_equal_the_plain_solvers(kind):
-    P, x0, n, m, T, B = _lqr_case(1)
+    P, x0, n, m, T, B, _ = _lqr_case(1)
     xs, us = np.repeat(x0[:, None, :], T + 1, 1), np.zeros((B, T, m))
     a = ol.OracleBatch("lqr", kind, T, n, m, P, x0)
     b = ol.OracleBatch("lqr", kind[3:], T, n, m, P, x0)
@@ -106,33 +128,26 @@ def test_box_solvers_without_limits_equal_the_plain_solvers(kind):
 
 
 @pytest.mark.parametrize("kind", ["boxddp", "boxfddp"])
-def test_box_solvers_respect_limits_and_reach_the_bounded_optimum(kind):
-    """LQR with control limits is a convex QP in us: the control-limited solvers must end inside the box at a cost no
-    worse than scipy's L-BFGS-B on the same problem (condensed through the rollout) and never above the clamped
-    unconstrained solution."""
-    P, x0, n, m, T, B = _lqr_case(2)
-    lim = 0.15
+@pytest.mark.parametrize("fu,lim", [(0.3, 0.3), (0.3, 0.6), (1.0, 0.15)])
+def test_box_solvers_reach_the_bounded_optimum_of_scipy(kind, fu, lim):
+    """Third-party pin at the solver level: an LQR problem with control limits is a convex box QP in us. The
+    control-limited solvers must end inside the box, with active bounds, at the optimum scipy's L-BFGS-B finds for the
+    same problem (objective + adjoint gradient written independently in NumPy above)."""
+    P, x0, n, m, T, B, M = _lqr_case(3, fu=fu)
     lb, ub = -lim * np.ones((B, m)), lim * np.ones((B, m))
     xs, us = np.repeat(x0[:, None, :], T + 1, 1), np.zeros((B, T, m))
     s = ol.OracleBatch("lqr", kind, T, n, m, P, x0)
     s.set_u_bounds(lb, ub)
     s.solve(xs, us, 100, False, 1e-9)
     sc = s.scalars()
+    assert np.all(sc["converged"] == 1)
     U = s.get_all("us")
-    assert np.all(U >= -lim - 1e-12) and np.all(U <= lim + 1e-12)
-    assert (np.abs(np.abs(U) - lim) < 1e-12).any(), "no active bound: the case does not exercise the box QP"
-    plain = ol.OracleBatch("lqr", "fddp", T, n, m, P, x0)
+    assert np.all(U >= -lim) and np.all(U <= lim)
+    assert (np.abs(U) == lim).mean() > 0.1, "too few active bounds: the case does not exercise the box QP"
     for b in range(B):
-        def total_cost(uflat, b=b):
-            one = ol.OracleBatch("lqr", "ddp", T, n, m, P[b], x0[b:b + 1])
-            u = uflat.reshape(1, T, m)
-            one.set_candidate(xs[b:b + 1], u, False)
-            one.calc()
-            X = np.concatenate([x0[b:b + 1], np.stack([one.get("xnext", 0, t) for t in range(T)])])
-            one.set_candidate(X[None], u, True)
-            return one.calc()[0]
-        ref = minimize(total_cost, np.zeros(T * m), method="L-BFGS-B", bounds=[(-lim, lim)] * (T * m),
-                       options=dict(maxiter=500, ftol=1e-15, gtol=1e-10))
-        assert sc["cost"][b] <= ref.fun * (1 + 1e-6) + 1e-9, (sc["cost"][b], ref.fun)
-        # feasible, and the reported cost is the cost of the rollout of us
-        assert abs(total_cost(U[b].ravel()) - sc["cost"][b]) <= 1e-9 * max(1.0, abs(sc["cost"][b]))
+        ref = minimize(_cost_and_gradient, np.zeros(T * m), args=(M[b], x0[b], T, m), jac=True, method="L-BFGS-B",
+                       bounds=[(-lim, lim)] * (T * m), options=dict(maxiter=5000, ftol=1e-16, gtol=1e-12))
+        mine = _cost_and_gradient(U[b].ravel(), M[b], x0[b], T, m)[0]
+        np.testing.assert_allclose(sc["cost"][b], mine, rtol=1e-12)        # reported cost = cost of the rollout of us
+        np.testing.assert_allclose(mine, ref.fun, rtol=1e-9)              # = the bounded optimum
+        np.testing.assert_allclose(U[b].ravel(), ref.x, atol=2e-5)

@@ -11,6 +11,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
+from .base import ActionDataAbstract, ActionModelAbstract, StateVector, _f64  # noqa: F401
 from .arm import ArmActionModel, RevoluteChain, synthetic_arm  # noqa: F401
 from ._lib import CgxError, check, dptr, lib  # noqa: F401
 
@@ -18,20 +19,13 @@ MODEL_LQR, MODEL_UNICYCLE, MODEL_ARM = 0, 1, 2
 SOLVER_DDP, SOLVER_FDDP = 0, 1
 
 
-def _f64(a, shape=None):
-    a = np.ascontiguousarray(a, dtype=np.float64)
-    if shape is not None:
-        a = a.reshape(shape)
-    return a
-
-
-class ActionModelUnicycle(object):
+class ActionModelUnicycle(ActionModelAbstract):
     """ActionModelUnicycle (include/crocoddyl/core/actions/unicycle.hxx:13-73): nx = 3, nu = 2, dt = 0.1,
     costWeights = (10, 1)."""
     kind = MODEL_UNICYCLE
-    nx, ndx, nu, nr = 3, 3, 2, 5
 
     def __init__(self):
+        self._init_abstract(3, 2, 5)
         self.dt = 0.1
         self.costWeights = np.array([10., 1.])
 
@@ -39,15 +33,13 @@ class ActionModelUnicycle(object):
         return np.array([self.dt, self.costWeights[0], self.costWeights[1]], dtype=np.float64)
 
 
-class ActionModelLQR(object):
+class ActionModelLQR(ActionModelAbstract):
     """ActionModelLQR(nx, nu, driftFree=True) (include/crocoddyl/core/actions/lqr.hxx:14-70). Every matrix may
     carry a leading batch dimension ([B, ...]) to give each problem of the batch its own model."""
     kind = MODEL_LQR
 
     def __init__(self, nx, nu, driftFree=True):
-        self.nx = self.ndx = int(nx)
-        self.nu = int(nu)
-        self.nr = 0
+        self._init_abstract(nx, nu, 0)
         self.driftFree = bool(driftFree)
         self.Fx = np.eye(nx)
         self.Fu = np.eye(nx, nu)
@@ -92,18 +84,20 @@ class ActionModelLQR(object):
 class ShootingProblem(object):
     """ShootingProblem(x0, runningModels, terminalModel) (include/crocoddyl/core/optctrl/shooting.hpp:48-63).
 
-    x0 is [nx] (one problem) or [B, nx] (a batch). The path accelerated here aliases ONE model object into
-    all running nodes and the terminal node, as the reference's benchmarks do
-    (benchmark/unicycle-optctrl.cpp:25-32); anything else raises."""
+    x0 is [nx] (one problem) or [B, nx] (a batch). ONE running model object is aliased into all T running nodes, as
+    the reference's benchmarks and examples do (benchmark/unicycle-optctrl.cpp:25-32, examples/arm_manipulation.py:63);
+    the terminal model may be a different object of the same family and dimensions (its own weights, dt, ...: the
+    terminal cost = gripperPose only of examples/arm_manipulation.py:41-57 is expressible). Distinct running models
+    per node raise."""
 
     def __init__(self, x0, runningModels, terminalModel):
         if len(runningModels) == 0:
             raise ValueError("Invalid argument: at least one running model is needed")
         model = runningModels[0]
-        if any(m is not model for m in runningModels) or terminalModel is not model:
-            term_ok = getattr(model, "terminal_of", None) is not None and terminalModel is model.terminal_of
-            if any(m is not model for m in runningModels) or not term_ok:
-                raise CgxError(-3, "only problems that alias one model into every node are supported")
+        if any(m is not model for m in runningModels):
+            raise CgxError(-3, "only problems that alias one running model into every node are supported")
+        if terminalModel.kind != model.kind or terminalModel.nx != model.nx or terminalModel.nu != model.nu:
+            raise CgxError(-3, "the terminal model must be of the running model's family and dimensions")
         self.model = model
         self.runningModels = list(runningModels)
         self.terminalModel = terminalModel
@@ -115,13 +109,28 @@ class ShootingProblem(object):
         self.B, self.T = x0.shape[0], len(runningModels)
         self.nx, self.ndx, self.nu_max = model.nx, model.ndx, model.nu
         params = _f64(model.params())
-        per = params.ndim == 2
+        tparams = params if terminalModel is model else _f64(terminalModel.params())
+        per = params.ndim == 2 or tparams.ndim == 2
+        if per:  # per-problem blocks: both blocks get the batch dimension
+            params = np.ascontiguousarray(np.broadcast_to(params, (self.B, params.shape[-1])))
+            tparams = np.ascontiguousarray(np.broadcast_to(tparams, (self.B, tparams.shape[-1])))
         if per and params.shape[0] != self.B:
             raise CgxError(-1, "Invalid argument: model batch dimension differs from x0's")
         self._h = C.c_void_p()
-        self._keep = (params, x0)
+        self._keep = (params, x0, tparams)
         check(lib().cgx_problem_create(C.byref(self._h), model.kind, self.B, self.T, self.nx, model.nu, dptr(params),
                                        params.shape[-1], int(per), dptr(x0)))
+        check(lib().cgx_problem_set_terminal_params(self._h, dptr(tparams), tparams.shape[-1]))
+        lb, ub = getattr(model, "u_lb", None), getattr(model, "u_ub", None)
+        if lb is not None and (np.isfinite(lb).any() or np.isfinite(ub).any()):
+            self.set_u_bounds(lb, ub)
+
+    def set_u_bounds(self, lb, ub):
+        """set_u_lb / set_u_ub of the running model (action-base.hxx:117-140): [nu] shared or [B, nu]."""
+        lb, ub = _f64(lb), _f64(ub)
+        if lb.shape != ub.shape or lb.shape[-1] != self.nu_max or (lb.ndim == 2 and lb.shape[0] != self.B):
+            raise CgxError(-1, "Invalid argument: lower bound has wrong dimension (it should be %d)" % self.nu_max)
+        check(lib().cgx_problem_set_u_bounds(self._h, dptr(lb), dptr(ub), int(lb.ndim == 2)))
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -337,7 +346,8 @@ class SolverDDP(object):
     def _shape(self, name):
         n, m = self.problem.ndx, self.problem.nu_max
         return {"xs": (n,), "us": (m,), "xs_try": (n,), "us_try": (m,), "fs": (n,), "K": (m, n), "k": (m,),
-                "Vx": (n,), "Vxx": (n, n), "Qxx": (n, n), "Qxu": (n, m), "Quu": (m, m), "Qx": (n,), "Qu": (m,)}[name]
+                "Vx": (n,), "Vxx": (n, n), "Qxx": (n, n), "Qxu": (n, m), "Quu": (m, m), "Qx": (n,), "Qu": (m,),
+                "Quu_inv": (m, m)}[name]
 
     def get(self, name):
         """[B, nt, *shape] array of a per-node field (matrices converted from column-major)."""
@@ -422,6 +432,19 @@ class SolverFDDP(SolverDDP):
     """SolverFDDP(problem) (include/crocoddyl/core/solvers/fddp.hpp:50-100)."""
     _kind = SOLVER_FDDP
     th_acceptNegStep = _param_prop("th_acceptnegstep")
+
+
+class SolverBoxDDP(SolverDDP):
+    """SolverBoxDDP(problem) (include/crocoddyl/core/solvers/box-ddp.hpp, src/core/solvers/box-ddp.cpp): control-limited
+    DDP — BoxQP in computeGains, clamp in forwardPass; reads u_lb / u_ub of the running model."""
+    _kind = 2
+    Quu_inv = _field_prop("Quu_inv")
+
+
+class SolverBoxFDDP(SolverFDDP):
+    """SolverBoxFDDP(problem) (box-fddp.hpp, src/core/solvers/box-fddp.cpp)."""
+    _kind = 3
+    Quu_inv = _field_prop("Quu_inv")
 
 
 def device_count():

@@ -34,6 +34,10 @@ SIGNATURES = {
     "cgx_version": (_cp, []),
     "cgx_problem_create": (C.c_int, [_vpp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _dp, C.c_long, C.c_int, _dp]),
     "cgx_problem_destroy": (C.c_int, [_vp]),
+    "cgx_problem_set_terminal_params": (C.c_int, [_vp, _dp, C.c_long]),
+    "cgx_problem_get_terminal_params": (C.c_int, [_vp, _dp]),
+    "cgx_problem_set_u_bounds": (C.c_int, [_vp, _dp, _dp, C.c_int]),
+    "cgx_problem_get_u_bounds": (C.c_int, [_vp, _dp, _dp, _ip, _ip]),
     "cgx_problem_set_x0": (C.c_int, [_vp, _dp]),
     "cgx_problem_get_x0": (C.c_int, [_vp, _dp]),
     "cgx_problem_dims": (C.c_int, [_vp, _ip, _ip, _ip, _ip, _ip]),

@@ -14,7 +14,11 @@ Parameter block (doubles) = 32 + 25 nv, see include/crocoddyl_b200.h "ARM":
 """
 import numpy as np
 
+from .base import ActionModelAbstract
+
 MODEL_ARM = 2
+
+
 ARM_HEADER, ARM_PER_JOINT = 32, 25
 
 
@@ -44,7 +48,7 @@ def synthetic_arm(nv=7):
     return RevoluteChain(axes, R, p, [2.0] * nv, [(0., 0., 0.15)] * nv, [np.diag([0.02, 0.02, 0.005])] * nv)
 
 
-class ArmActionModel(object):
+class ArmActionModel(ActionModelAbstract):
     """IntegratedActionModelEuler(DifferentialActionModelFreeFwdDynamics(...), dt) (euler.hxx, free-fwddyn.hxx) with
     the cost sum of benchmark/factory/arm.hpp:62-74. `terminal_model` is the same differential model with dt = 0."""
     kind = MODEL_ARM
@@ -53,9 +57,7 @@ class ArmActionModel(object):
                  Mref_p=(0., 0., 0.4), w_gripperPose=1., w_xReg=1e-4, w_uReg=1e-4, _terminal_of=None):
         self.chain = chain
         self.nv = chain.nv
-        self.nx = self.ndx = 2 * chain.nv
-        self.nu = chain.nv
-        self.nr = 6 + self.ndx + self.nu
+        self._init_abstract(2 * chain.nv, chain.nv, 6 + 2 * chain.nv + chain.nv, nq=chain.nv)
         self.dt = float(dt)
         self.frame_parent = chain.nv - 1 if frame_parent is None else int(frame_parent)
         self.frame_R = np.eye(3) if frame_R is None else np.asarray(frame_R, dtype=np.float64)

@@ -69,6 +69,7 @@ struct ArmModel {
   static constexpr int kDirMinBlocks = CGX_ARM_DIR_MINBLOCKS, kFwdMinBlocks = CGX_ARM_FWD_MINBLOCKS;
   static constexpr int kN = 2 * NV, kM = NV;  // compile-time node sizes for the warp-level backward pass
   const double* params;
+  const double* tparams;  // terminal model's block (default: the running block with dt = 0)
 
   // host side: device address of a derivative matrix of node t of problem b
   template <class PD>
@@ -85,7 +86,11 @@ struct ArmModel {
     arm_quasi_static_kernel<NV><<<(c.B + 127) / 128, 128, 0, stream>>>(c.params, c.nparams, c.per_problem, c.B, d_x, d_u);
     ++be.last_launches;
   }
-  __device__ void load(const CtaCtx& c, int b) { params = c.params + (c.per_problem ? (size_t)b * c.nparams : 0); }
+  __device__ void load(const CtaCtx& c, int b) {
+    const size_t off = c.per_problem ? (size_t)b * c.nparams : 0;
+    params = c.params + off;
+    tparams = c.tparams + off;
+  }
   __device__ NodeMats mats(const CtaCtx& c, int b, int t) const {
     const size_t n = c.n, m = c.m, node = (size_t)b * (c.T + 1) + t;
     return NodeMats{c.d_Fx + node * n * n, c.d_Fu + node * n * m, c.d_Lxx + node * n * n, nullptr,
@@ -102,7 +107,7 @@ struct ArmModel {
 #pragma unroll
       for (int i = 0; i < NV; ++i) u[i] = us[(size_t)t * NV + i];
     }
-    c.d_cost[node] = arm_calc_node_dev<NV>(params, t == T, x, t < T ? u : nullptr, xn);
+    c.d_cost[node] = arm_calc_node_dev<NV>(t == T ? tparams : params, t == T, x, t < T ? u : nullptr, xn);
 #pragma unroll
     for (int i = 0; i < 2 * NV; ++i) c.d_xnext[node * 2 * NV + i] = xn[i];
   }
@@ -117,7 +122,7 @@ struct ArmModel {
 #pragma unroll
       for (int i = 0; i < NV; ++i) u[i] = us[(size_t)t * NV + i];
     }
-    arm_calcdiff_node_dev<NV>(params, t == T, x, t < T ? u : nullptr, c.d_Fx + node * n * n, c.d_Fu + node * n * m,
+    arm_calcdiff_node_dev<NV>(t == T ? tparams : params, t == T, x, t < T ? u : nullptr, c.d_Fx + node * n * n, c.d_Fu + node * n * m,
                               c.d_Lx + node * n, c.d_Lu + node * m, c.d_Lxx + node * n * n, c.d_Luu + node * m * m);
   }
   __device__ void calc_all(const CtaCtx& c, int b, const double* xs, const double* us) const {
@@ -130,7 +135,7 @@ struct ArmModel {
   // it cooperatively (arm_warp.cuh), the other warps of the block wait
   __device__ void calc_block(const double* x, const double* u, double* xnext, double*, double* cost_out) const {
     __shared__ ArmWarpSmem<NV> W;
-    if (threadIdx.x < 32) arm_calc_warp<NV>(params, u == nullptr, x, u, xnext, cost_out, W);
+    if (threadIdx.x < 32) arm_calc_warp<NV>(u == nullptr ? tparams : params, u == nullptr, x, u, xnext, cost_out, W);
     __syncthreads();
   }
 };

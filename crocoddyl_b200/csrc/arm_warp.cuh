@@ -158,7 +158,7 @@ __device__ void arm_calc_warp(const double* params, bool terminal, const double*
   }
   __syncwarp();
   // S4: acceleration recursion, redundantly on every lane; lane i writes joint i of xnext (euler.hxx:65-74)
-  double dt = terminal ? 0. : P.dt();
+  double dt = P.dt();  // the terminal node has its own block (dt = 0 by default, benchmark/factory/arm.hpp:89-90)
   if (dt < 0.) dt = 1e-3;
   {
     const V3 g = P.gravity();

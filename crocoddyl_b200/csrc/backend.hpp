@@ -49,6 +49,18 @@ struct ProblemDesc {
   std::vector<double> h_x0;      // [B][nx]
   double* d_params = nullptr;    // device copy, same layout
   double* d_x0 = nullptr;        // [B][nx]
+  // terminal model (shooting.hpp:48-63): same layout / count / per-problem-ness as the running block; by default a copy
+  // of it (arm: with dt = 0, benchmark/factory/arm.hpp:89-90). Always allocated: kernels read it unconditionally.
+  std::vector<double> h_tparams;
+  double* d_tparams = nullptr;
+  // control limits of the running model (action-base.hxx:117-140): [nb][nu] each, nb = B if bounds_per_problem else 1;
+  // d_haslim[nb] = has_control_limits. Always allocated (defaults -inf / +inf / 0).
+  int bounds_per_problem = 0;
+  std::vector<double> h_ulb, h_uub;
+  std::vector<int> h_haslim;
+  double* d_ulb = nullptr;
+  double* d_uub = nullptr;
+  int* d_haslim = nullptr;
 };
 
 // field description for accessors

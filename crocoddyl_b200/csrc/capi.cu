@@ -3,6 +3,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <limits>
 #include <string>
 #include "../../include/crocoddyl_b200.h"
 #include "backend.hpp"
@@ -202,6 +203,24 @@ int cgx_problem_create(cgx_problem_t* out, int kind, int B, int T, int nx, int n
     p->d.d_x0 = dalloc<double>((size_t)B * nx);
     CGX_CUDA(cudaMemcpy(p->d.d_params, params, np * sizeof(double), cudaMemcpyHostToDevice));
     CGX_CUDA(cudaMemcpy(p->d.d_x0, x0s, (size_t)B * nx * sizeof(double), cudaMemcpyHostToDevice));
+    // terminal block: the running one (arm: with dt = 0, benchmark/factory/arm.hpp:89-90) until
+    // cgx_problem_set_terminal_params replaces it
+    p->d.h_tparams = p->d.h_params;
+    if (kind == CGX_MODEL_ARM)
+      for (size_t b = 0; b < (per_problem_params ? (size_t)B : 1); ++b) p->d.h_tparams[b * nparams] = 0.;
+    p->d.d_tparams = dalloc<double>(np);
+    CGX_CUDA(cudaMemcpy(p->d.d_tparams, p->d.h_tparams.data(), np * sizeof(double), cudaMemcpyHostToDevice));
+    // control limits: unbounded (action-base.hxx:19-22)
+    const size_t nb = (size_t)B * (nu ? nu : 1);
+    p->d.h_ulb.assign(nb, -std::numeric_limits<double>::infinity());
+    p->d.h_uub.assign(nb, std::numeric_limits<double>::infinity());
+    p->d.h_haslim.assign(B, 0);
+    p->d.d_ulb = dalloc<double>(nb);
+    p->d.d_uub = dalloc<double>(nb);
+    p->d.d_haslim = dalloc<int>(B);
+    CGX_CUDA(cudaMemcpy(p->d.d_ulb, p->d.h_ulb.data(), nb * sizeof(double), cudaMemcpyHostToDevice));
+    CGX_CUDA(cudaMemcpy(p->d.d_uub, p->d.h_uub.data(), nb * sizeof(double), cudaMemcpyHostToDevice));
+    CGX_CUDA(cudaMemset(p->d.d_haslim, 0, B * sizeof(int)));
   } catch (...) {
     cgx_problem_destroy(p);
     throw;
@@ -216,10 +235,69 @@ int cgx_problem_destroy(cgx_problem_t p) {
   delete p->pb;
   if (p->d.d_params) cudaFree(p->d.d_params);
   if (p->d.d_x0) cudaFree(p->d.d_x0);
+  if (p->d.d_tparams) cudaFree(p->d.d_tparams);
+  if (p->d.d_ulb) cudaFree(p->d.d_ulb);
+  if (p->d.d_uub) cudaFree(p->d.d_uub);
+  if (p->d.d_haslim) cudaFree(p->d.d_haslim);
   if (p->d_tmp_xs) cudaFree(p->d_tmp_xs);
   if (p->d_tmp_us) cudaFree(p->d_tmp_us);
   if (p->d_tmp_cost) cudaFree(p->d_tmp_cost);
   delete p;
+  return CGX_OK;
+}
+
+int cgx_problem_set_terminal_params(cgx_problem_t p, const double* tparams, long nparams) {
+  CGX_TRY
+  if (!p || !tparams) throw InvalidArg("Invalid argument: NULL");
+  if (nparams != p->d.nparams)
+    throw InvalidArg("Invalid argument: terminal params have wrong size (it should be " + std::to_string(p->d.nparams) + ")");
+  const size_t np = (size_t)nparams * (p->d.per_problem_params ? p->d.B : 1);
+  p->d.h_tparams.assign(tparams, tparams + np);
+  CGX_CUDA(cudaDeviceSynchronize());  // no kernel of a live solver may be reading the old block
+  CGX_CUDA(cudaMemcpy(p->d.d_tparams, tparams, np * sizeof(double), cudaMemcpyHostToDevice));
+  return CGX_OK;
+  CGX_CATCH
+}
+int cgx_problem_get_terminal_params(cgx_problem_t p, double* tparams) {
+  if (!p || !tparams) return fail(CGX_ERR_INVALID, "Invalid argument: NULL");
+  std::memcpy(tparams, p->d.h_tparams.data(), p->d.h_tparams.size() * sizeof(double));
+  return CGX_OK;
+}
+
+int cgx_problem_set_u_bounds(cgx_problem_t p, const double* lb, const double* ub, int per_problem) {
+  CGX_TRY
+  if (!p || !lb || !ub) throw InvalidArg("Invalid argument: NULL");
+  const int B = p->d.B, nu = p->d.nu;
+  if (nu == 0) throw InvalidArg("Invalid argument: lower bound has wrong dimension (it should be 0)");
+  for (int b = 0; b < B; ++b) {
+    const double* l = lb + (per_problem ? (size_t)b * nu : 0);
+    const double* u = ub + (per_problem ? (size_t)b * nu : 0);
+    bool fl = false, fu = false;
+    for (int i = 0; i < nu; ++i) {
+      if (std::isnan(l[i]) || std::isnan(u[i])) throw InvalidArg("Invalid argument: NaN in the control bounds");
+      p->d.h_ulb[(size_t)b * nu + i] = l[i];
+      p->d.h_uub[(size_t)b * nu + i] = u[i];
+      fl = fl || std::isfinite(l[i]);
+      fu = fu || std::isfinite(u[i]);
+    }
+    p->d.h_haslim[b] = (fl && fu) ? 1 : 0;  // action-base.hxx:142-144
+  }
+  p->d.bounds_per_problem = per_problem != 0;
+  CGX_CUDA(cudaDeviceSynchronize());
+  CGX_CUDA(cudaMemcpy(p->d.d_ulb, p->d.h_ulb.data(), (size_t)B * nu * sizeof(double), cudaMemcpyHostToDevice));
+  CGX_CUDA(cudaMemcpy(p->d.d_uub, p->d.h_uub.data(), (size_t)B * nu * sizeof(double), cudaMemcpyHostToDevice));
+  CGX_CUDA(cudaMemcpy(p->d.d_haslim, p->d.h_haslim.data(), (size_t)B * sizeof(int), cudaMemcpyHostToDevice));
+  return CGX_OK;
+  CGX_CATCH
+}
+int cgx_problem_get_u_bounds(cgx_problem_t p, double* lb, double* ub, int* per_problem, int* has_control_limits) {
+  if (!p) return fail(CGX_ERR_INVALID, "Invalid argument: NULL");
+  const size_t cnt = (size_t)(p->d.bounds_per_problem ? p->d.B : 1) * p->d.nu;
+  if (lb) std::memcpy(lb, p->d.h_ulb.data(), cnt * sizeof(double));
+  if (ub) std::memcpy(ub, p->d.h_uub.data(), cnt * sizeof(double));
+  if (per_problem) *per_problem = p->d.bounds_per_problem;
+  if (has_control_limits)
+    for (int b = 0; b < (p->d.bounds_per_problem ? p->d.B : 1); ++b) has_control_limits[b] = p->d.h_haslim[b];
   return CGX_OK;
 }
 
@@ -329,13 +407,15 @@ int cgx_solver_create(cgx_solver_t* out, cgx_problem_t p, int solver_kind) {
   CGX_TRY
   if (!out || !p) throw InvalidArg("Invalid argument: NULL");
   *out = nullptr;
-  if (solver_kind != CGX_SOLVER_DDP && solver_kind != CGX_SOLVER_FDDP) throw InvalidArg("Invalid argument: solver kind");
+  if (solver_kind < CGX_SOLVER_DDP || solver_kind > CGX_SOLVER_BOXFDDP) throw InvalidArg("Invalid argument: solver kind");
   require_device();
   cgx_solver_s* s = new cgx_solver_s();
   s->p = p;
   try {
     s->be = make_backend(&p->d, solver_kind);
     default_opts(s->be->o);
+    // box-ddp.cpp:24-29 / box-fddp.cpp:24-29: the gradient of the Lagrangian is not available, looser default tolerance
+    if (solver_kind == CGX_SOLVER_BOXDDP || solver_kind == CGX_SOLVER_BOXFDDP) s->be->o.th_stop = 5e-5;
     s->be->configure();
     const size_t B = p->d.B, T = p->d.T;
     s->d_init_xs = dalloc<double>(B * (T + 1) * p->d.nx);
@@ -392,7 +472,8 @@ int cgx_solver_set_param(cgx_solver_t s, const char* name, double v) {
     if (!(0. < v && v <= 1.)) throw InvalidArg("Invalid argument: th_stepinc value should between 0 and 1.");
     o.th_stepinc = v;
   } else if (n == "th_acceptnegstep") {
-    if (s->be->solver_kind != CGX_SOLVER_FDDP) throw InvalidArg("Invalid argument: th_acceptnegstep is an FDDP parameter");
+    if (s->be->solver_kind != CGX_SOLVER_FDDP && s->be->solver_kind != CGX_SOLVER_BOXFDDP)
+      throw InvalidArg("Invalid argument: th_acceptnegstep is an FDDP parameter");
     if (v < 0.) throw InvalidArg("Invalid argument: th_acceptnegstep value has to be positive.");
     o.th_acceptnegstep = v;
   } else if (n == "regfactor") {

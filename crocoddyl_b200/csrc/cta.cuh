@@ -15,6 +15,7 @@
 #pragma once
 #include <stdexcept>
 #include <string>
+#include "boxqp.cuh"
 #include "common.cuh"
 
 namespace cgx {
@@ -47,6 +48,14 @@ struct CtaCtx {
   double* d_Lxu;
   double* d_Luu;
   const double* params;   // model parameter block(s)
+  const double* tparams;  // terminal model's block(s): same layout / count / per-problem-ness (shooting.hpp:48-63)
+  const double* u_lb;     // [B][m] control limits of the running model (action-base.hxx:117-140)
+  const double* u_ub;     // [B][m]
+  const int* has_limits;  // [B]
+  int box;                // 1 = SolverBoxDDP / SolverBoxFDDP (box-ddp.cpp, box-fddp.cpp)
+  double* Quu_inv;        // box only: [B][T][m*m]
+  double* box_work;       // box only: [B][box_gains_work_doubles(m)] scratch of the per-node box QP
+  int* box_iwork;         // box only: [B][box_gains_work_ints(m)]
   long nparams;
   int per_problem;
   const double* x0;       // [B][n]
@@ -66,6 +75,8 @@ struct NodeMats {
   const double* Luu;
   bool constant;  // the same for every running node of the problem (LQR): stage once
 };
+
+__device__ __forceinline__ int CTA_I_(const CtaCtx& c, int b, int slot) { return c.iscal[(size_t)slot * c.Bp + b]; }
 
 }  // namespace cgx
 #include "cta_small.cuh"
@@ -202,14 +213,29 @@ struct LqrModel {
   static constexpr bool kNodeKernel = false;
   static constexpr int kMinThreads = 64, kMaxThreads = 384, kMinBlocks = 1, kDirMinBlocks = 1, kFwdMinBlocks = 1;
   static constexpr int kN = 0, kM = 0;  // run-time sizes
-  const double *Fx, *Fu, *f0, *Lxx, *Lxu, *Luu, *lx, *lu;
-  bool drift_free;
+  // matrices of one ActionModelLQR inside its parameter block
+  struct Blk {
+    const double *Fx, *Fu, *f0, *Lxx, *Lxu, *Luu, *lx, *lu;
+    bool drift_free;
+    __device__ void set(const double* p, int n, int m) {
+      drift_free = p[0] != 0.;
+      Fx = p + 1;
+      Fu = Fx + n * n;
+      f0 = Fu + n * m;
+      Lxx = f0 + n;
+      Lxu = Lxx + n * n;
+      Luu = Lxu + n * m;
+      lx = Luu + m * m;
+      lu = lx + n;
+    }
+  };
+  Blk run, term;  // running nodes / terminal node (u == nullptr selects the terminal model: action-base.hxx:27-31)
   int n, m;
   // host side: device address of a constant derivative matrix (ActionDataLQR holds copies, lqr.hxx:65-69)
   template <class PD>
-  static const double* node_matrix(const CtaCtx& c, const PD*, const std::string& name, int b, int) {
+  static const double* node_matrix(const CtaCtx& c, const PD*, const std::string& name, int b, int t) {
     const size_t n = c.n, m = c.m;
-    const double* p = c.params + (c.per_problem ? (size_t)b * c.nparams : 0);
+    const double* p = (t == c.T ? c.tparams : c.params) + (c.per_problem ? (size_t)b * c.nparams : 0);
     if (name == "Fx") return p + 1;
     if (name == "Fu") return p + 1 + n * n;
     if (name == "Lxx") return p + 1 + n * n + n * m + n;
@@ -223,62 +249,60 @@ struct LqrModel {
   __device__ void load(const CtaCtx& c, int b) {
     n = c.n;
     m = c.m;
-    const double* p = c.params + (c.per_problem ? (size_t)b * c.nparams : 0);
-    drift_free = p[0] != 0.;
-    Fx = p + 1;
-    Fu = Fx + n * n;
-    f0 = Fu + n * m;
-    Lxx = f0 + n;
-    Lxu = Lxx + n * n;
-    Luu = Lxu + n * m;
-    lx = Luu + m * m;
-    lu = lx + n;
+    const size_t off = c.per_problem ? (size_t)b * c.nparams : 0;
+    run.set(c.params + off, n, m);
+    term.set(c.tparams + off, n, m);
   }
-  __device__ NodeMats mats(const CtaCtx&, int, int) const { return NodeMats{Fx, Fu, Lxx, Lxu, Luu, true}; }
+  __device__ NodeMats mats(const CtaCtx& c, int, int t) const {
+    const Blk& q = t == c.T ? term : run;
+    return NodeMats{q.Fx, q.Fu, q.Lxx, q.Lxu, q.Luu, true};
+  }
 
   // calc of one node by ONE thread, in the oracle's operation order (lqr.hxx:31-49). u == nullptr: zeros.
   __device__ double calc_serial(const double* x, const double* u, double* xnext) const {
+    const Blk& q = u ? run : term;
     for (int i = 0; i < n; ++i) {
       double a = 0., bsum = 0.;
-      for (int j = 0; j < n; ++j) a += Fx[i + n * j] * x[j];
+      for (int j = 0; j < n; ++j) a += q.Fx[i + n * j] * x[j];
       if (u)
-        for (int j = 0; j < m; ++j) bsum += Fu[i + n * j] * u[j];
-      xnext[i] = drift_free ? (a + bsum) : (a + bsum + f0[i]);
+        for (int j = 0; j < m; ++j) bsum += q.Fu[i + n * j] * u[j];
+      xnext[i] = q.drift_free ? (a + bsum) : (a + bsum + q.f0[i]);
     }
     double xLx = 0., uLu = 0., xLu = 0., lxx_ = 0., luu_ = 0.;
     for (int i = 0; i < n; ++i) {
       double s = 0., s2 = 0.;
-      for (int j = 0; j < n; ++j) s += Lxx[i + n * j] * x[j];
+      for (int j = 0; j < n; ++j) s += q.Lxx[i + n * j] * x[j];
       if (u)
-        for (int j = 0; j < m; ++j) s2 += Lxu[i + n * j] * u[j];
+        for (int j = 0; j < m; ++j) s2 += q.Lxu[i + n * j] * u[j];
       xLx += x[i] * s;
       xLu += x[i] * s2;
-      lxx_ += lx[i] * x[i];
+      lxx_ += q.lx[i] * x[i];
     }
     if (u)
       for (int i = 0; i < m; ++i) {
         double s = 0.;
-        for (int j = 0; j < m; ++j) s += Luu[i + m * j] * u[j];
+        for (int j = 0; j < m; ++j) s += q.Luu[i + m * j] * u[j];
         uLu += u[i] * s;
-        luu_ += lu[i] * u[i];
+        luu_ += q.lu[i] * u[i];
       }
     return 0.5 * xLx + 0.5 * uLu + xLu + lxx_ + luu_;
   }
   // Lx, Lu of one node by one thread (lqr.hxx:63-64); the five matrices are the model's constants
   __device__ void calcdiff_serial(const double* x, const double* u, double* Lx, double* Lu) const {
+    const Blk& q = u ? run : term;
     for (int i = 0; i < n; ++i) {
       double a = 0., bsum = 0.;
-      for (int j = 0; j < n; ++j) a += Lxx[i + n * j] * x[j];
+      for (int j = 0; j < n; ++j) a += q.Lxx[i + n * j] * x[j];
       if (u)
-        for (int j = 0; j < m; ++j) bsum += Lxu[i + n * j] * u[j];
-      Lx[i] = lx[i] + a + bsum;
+        for (int j = 0; j < m; ++j) bsum += q.Lxu[i + n * j] * u[j];
+      Lx[i] = q.lx[i] + a + bsum;
     }
     for (int i = 0; i < m; ++i) {
       double cc = 0., e = 0.;
-      for (int j = 0; j < n; ++j) cc += Lxu[j + n * i] * x[j];
+      for (int j = 0; j < n; ++j) cc += q.Lxu[j + n * i] * x[j];
       if (u)
-        for (int j = 0; j < m; ++j) e += Luu[i + m * j] * u[j];
-      Lu[i] = lu[i] + cc + e;
+        for (int j = 0; j < m; ++j) e += q.Luu[i + m * j] * u[j];
+      Lu[i] = q.lu[i] + cc + e;
     }
   }
   // all nodes of the problem at once: one node per thread (ShootingProblem::calc, shooting.hxx:133-161)
@@ -299,28 +323,29 @@ struct LqrModel {
   // calc of one node by the whole block (rollout): x, u in shared memory; writes xnext (shared), returns the
   // cost to thread 0 through *cost_out (shared). scratch: >= 2n+m doubles of shared memory.
   __device__ void calc_block(const double* x, const double* u, double* xnext, double* scratch, double* cost_out) const {
+    const Blk& q = u ? run : term;
     double* Lxx_x = scratch;
     double* Lxu_u = scratch + n;
     double* Luu_u = scratch + 2 * n;
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
       double a = 0., bsum = 0., s = 0., s2 = 0.;
       for (int j = 0; j < n; ++j) {
-        a += Fx[i + n * j] * x[j];
-        s += Lxx[i + n * j] * x[j];
+        a += q.Fx[i + n * j] * x[j];
+        s += q.Lxx[i + n * j] * x[j];
       }
       if (u)
         for (int j = 0; j < m; ++j) {
-          bsum += Fu[i + n * j] * u[j];
-          s2 += Lxu[i + n * j] * u[j];
+          bsum += q.Fu[i + n * j] * u[j];
+          s2 += q.Lxu[i + n * j] * u[j];
         }
-      xnext[i] = drift_free ? (a + bsum) : (a + bsum + f0[i]);
+      xnext[i] = q.drift_free ? (a + bsum) : (a + bsum + q.f0[i]);
       Lxx_x[i] = s;
       Lxu_u[i] = s2;
     }
     if (u)
       for (int i = threadIdx.x; i < m; i += blockDim.x) {
         double s = 0.;
-        for (int j = 0; j < m; ++j) s += Luu[i + m * j] * u[j];
+        for (int j = 0; j < m; ++j) s += q.Luu[i + m * j] * u[j];
         Luu_u[i] = s;
       }
     __syncthreads();
@@ -329,12 +354,12 @@ struct LqrModel {
       for (int i = 0; i < n; ++i) {
         xLx += x[i] * Lxx_x[i];
         xLu += x[i] * Lxu_u[i];
-        lxx_ += lx[i] * x[i];
+        lxx_ += q.lx[i] * x[i];
       }
       if (u)
         for (int i = 0; i < m; ++i) {
           uLu += u[i] * Luu_u[i];
-          luu_ += lu[i] * u[i];
+          luu_ += q.lu[i] * u[i];
         }
       *cost_out = 0.5 * xLx + 0.5 * uLu + xLu + lxx_ + luu_;
     }
@@ -527,6 +552,23 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, b
       for (int i = tid; i < n; i += P) c.Qx[rnode * n + i] = sm.Qx[i];
       for (int i = tid; i < m; i += P) c.Qu[rnode * m + i] = sm.Qu[i];
     }
+    // SolverBoxDDP/BoxFDDP::computeGains (box-ddp.cpp:46-74): box QP on the control step when the model has control
+    // limits and the candidate is feasible (one thread; work arrays in the problem's global scratch)
+    const bool boxed = c.box && is_feasible && c.has_limits[b] != 0;
+    if (boxed) {
+      if (tid == 0) {
+        const double* u_t = c.us[CTA_I_(c, b, I_CUR)] + rnode * m;
+        for (int i = 0; i < m; ++i) sm.kg[i] = c.k[rnode * m + i];  // k_[t] of the previous backward pass (warm start)
+        *sm.flag = box_compute_gains(n, m, sm.Quu, ldm, sm.Qu, sm.Qxu, ldn, u_t, c.u_lb + (size_t)b * m,
+                                     c.u_ub + (size_t)b * m, sm.Kg, ldm, sm.kg, c.Quu_inv + rnode * m * m, c.o,
+                                     c.box_work + (size_t)b * box_gains_work_doubles(m),
+                                     c.box_iwork + (size_t)b * box_gains_work_ints(m));
+      }
+      __syncthreads();
+      if (*sm.flag) return 1;
+      if (full)
+        for (int i = tid; i < m; i += P) c.Qu[rnode * m + i] = sm.Qu[i];  // get_Qu returns the clamped gradient
+    } else {
     // computeGains (ddp.cpp:298-310): unblocked lower LLT by warp 0
     if (tid < 32) {
       for (int e = tid; e < m * m; e += 32) sm.Lc[(e % m) + ldm * (e / m)] = sm.Quu[(e % m) + ldm * (e / m)];
@@ -566,6 +608,7 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, b
         r[i] = s / sm.Lc[i + ldm * i];
       }
     }
+    }  // !boxed
     __syncthreads();
     for (int i = tid; i < m; i += P) {
       double s = 0.;
@@ -682,6 +725,12 @@ __device__ int cta_forward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, in
   const bool closed = !fddp || is_feasible || (alpha == 1.);
   const bool use_w = fddp && !is_feasible;
   const double am1 = alpha - 1.;
+  // SolverBoxDDP::forwardPass keeps the gap of the TERMINAL node only (box-ddp.cpp:121-125); both box solvers clamp
+  // the control to the model's limits (box-ddp.cpp:95-97, box-fddp.cpp:96-98)
+  const bool term_open = c.box && !fddp && !(is_feasible || (alpha == 1.));
+  const bool clamp = c.box && c.has_limits[b] != 0;
+  const double* u_lb = c.u_lb + (size_t)b * m;
+  const double* u_ub = c.u_ub + (size_t)b * m;
   const double* xs = c.xs[cur] + (size_t)b * (T + 1) * n;
   const double* us = c.us[cur] + (size_t)b * T * m;
   double* xt_ = (tb ? tb->xs : c.xs[cur ^ 1]) + (size_t)b * (T + 1) * n;
@@ -733,7 +782,7 @@ __device__ int cta_forward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, in
       if (t < T) prefetch(t + 1, (t + 1) & 1);
     }
     for (int i = tid; i < n; i += P) {
-      const double xt = closed ? sm.xn[i] : sm.xn[i] + fs_t[i] * am1;
+      const double xt = (closed && !(term_open && t == T)) ? sm.xn[i] : sm.xn[i] + fs_t[i] * am1;
       sm.x[i] = xt;
       sm.dx[i] = xt - xs_t[i];
       xt_[(size_t)t * n + i] = xt;
@@ -743,7 +792,8 @@ __device__ int cta_forward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, in
       for (int i = tid; i < m; i += P) {
         double s = 0.;
         for (int j = 0; j < n; ++j) s += Kt[i + m * j] * sm.dx[j];
-        const double u = us_t[i] - kt[i] * alpha - s;
+        double u = us_t[i] - kt[i] * alpha - s;
+        if (clamp) u = fmin(fmax(u, u_lb[i]), u_ub[i]);
         sm.u[i] = u;
         ut_[(size_t)t * m + i] = u;
       }

@@ -35,9 +35,14 @@ struct CtaBackend : Backend {
     c.T = p->T;
     c.n = p->nx;
     c.m = p->nu;
-    c.fddp = sk == 1;
+    c.fddp = sk == 1 || sk == 3;  // SolverFDDP / SolverBoxFDDP
+    c.box = sk >= 2;              // SolverBoxDDP / SolverBoxFDDP
     c.model_kind = p->kind;
     c.params = p->d_params;
+    c.tparams = p->d_tparams;
+    c.u_lb = p->d_ulb;
+    c.u_ub = p->d_uub;
+    c.has_limits = p->d_haslim;
     c.nparams = p->nparams;
     c.per_problem = p->per_problem_params;
     c.x0 = p->d_x0;
@@ -143,6 +148,13 @@ struct CtaBackend : Backend {
       CGX_CUDA(cudaMemcpyAsync(c.scal, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice, stream));
       CGX_CUDA(cudaStreamSynchronize(stream));
       solver_allocated = true;
+    }
+    if (c.box && !c.Quu_inv) {
+      c.Quu_inv = alloc(B * T * m * m);
+      c.box_work = alloc(B * (size_t)box_gains_work_doubles((int)m));
+      int* iw = dalloc<int>(B * (size_t)box_gains_work_ints((int)m) + 1);
+      allocs.push_back(iw);
+      c.box_iwork = iw;
     }
     if (full && !c.Qxx) {
       c.Qxx = alloc(B * T * n * n);
@@ -280,6 +292,10 @@ struct CtaBackend : Backend {
     if (nme == "k") return {c.k, c.k, 0, m, T, false};
     if (nme == "Vx") return {c.Vx, c.Vx, 0, n, T + 1, false};
     if (nme == "Vxx") return {c.Vxx, c.Vxx, 0, n * n, T + 1, false};
+    if (nme == "Quu_inv") {  // SolverBoxDDP::get_Quu_inv (box-ddp.hpp)
+      if (!c.Quu_inv) throw Unsupported("Quu_inv is kept by the box solvers only");
+      return {c.Quu_inv, c.Quu_inv, 0, m * m, T, false};
+    }
     if (nme == "Qxx" || nme == "Qxu" || nme == "Quu" || nme == "Qx" || nme == "Qu") {
       if (!c.full || !c.Qxx)
         throw Unsupported("field " + nme + " is not kept with cgx_solver_set_storage(full = 0)");

@@ -8,6 +8,7 @@
 // Reference: src/core/solvers/ddp.cpp:180-253 (backwardPass), 298-310 (computeGains), 132-155 (stoppingCriteria,
 // expectedImprovement), src/core/solvers/fddp.cpp:126-147 (updateExpectedImprovement).
 #pragma once
+#include "boxqp.cuh"
 #include "common.cuh"
 
 namespace cgx {
@@ -179,6 +180,7 @@ __device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, bool is_f
         dq += q;
       }
       __syncwarp();
+      mats_staged = false;  // the terminal model may differ from the running one (shooting.hpp:48-63): restage
       if (T > 0) load_node(T - 1, S + pl.stage_sz);  // buffer 1
     }
     for (int t = T - 1; t >= 0; --t) {
@@ -294,7 +296,25 @@ __device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, bool is_f
         if (lane < m) c.Qu[rnode * m + lane] = Qu[lane];
       }
       // P3 + P4: computeGains (ddp.cpp:298-310): unblocked lower LLT of Quu, then K = Quu^-1 Qxu^T, k = Quu^-1 Qu.
-      if constexpr (KM > 0) {
+      // SolverBoxDDP/BoxFDDP::computeGains (box-ddp.cpp:46-74): box QP on the control step when the model has control
+      // limits and the candidate is feasible (lane 0; work arrays in the problem's global scratch)
+      const bool boxed = c.box && is_feasible && c.has_limits[b] != 0;
+      if (boxed) {
+        if (lane == 0) {
+          const double* u_t = c.us[CTA_I_(c, b, I_CUR)] + rnode * m;
+          for (int i = 0; i < m; ++i) kg[i] = c.k[rnode * m + i];  // k_[t] of the previous backward pass (warm start)
+          *flag = box_compute_gains(n, m, Quu, ldm, Qu, Qxu, ldn, u_t, c.u_lb + (size_t)b * m, c.u_ub + (size_t)b * m, Kg,
+                                    ldm, kg, c.Quu_inv + rnode * m * m, c.o,
+                                    c.box_work + (size_t)b * box_gains_work_doubles(m),
+                                    c.box_iwork + (size_t)b * box_gains_work_ints(m));
+        }
+        __syncwarp();
+        if (*flag) {
+          status = 1;
+          break;
+        }
+        if (full && lane < m) c.Qu[rnode * m + lane] = Qu[lane];  // get_Qu returns the clamped gradient
+      } else if constexpr (KM > 0) {
         // Compile-time m: EVERY lane factorises Quu redundantly in registers — no barriers and no shared-memory round
         // trips inside the serial chain — keeps the reciprocal pivots, and solves its own right-hand side in registers.
         // (ncu source page of the shared-memory version below: 36 % of the backward kernel's samples in these lines.)

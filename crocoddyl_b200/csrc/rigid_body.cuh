@@ -704,7 +704,7 @@ CGX_HD double arm_calc_node(const ArmParams& P, bool terminal, const double* x, 
   aba<NV>(P, x, x + NV, u, a, k);
   const FrameRes fr = frame_residual<NV>(P, k);
   const double cost = diff_cost<NV>(P, fr, x, u);
-  double dt = terminal ? 0. : P.dt();
+  double dt = P.dt();  // the terminal node has its own block (dt = 0 by default, benchmark/factory/arm.hpp:89-90)
   if (dt < 0.) dt = 1e-3;  // euler.hxx:27-31
   if (qdd_out) {
 #pragma unroll
@@ -741,7 +741,7 @@ template <int NV>
 CGX_HD void arm_calcdiff_node(const ArmParams& P, bool terminal, const double* x, const double* u, double* Fx, double* Fu,
                               double* Lx, double* Lu, double* Lxx, double* Luu) {
   constexpr int n = 2 * NV;
-  double dt = terminal ? 0. : P.dt();
+  double dt = P.dt();  // the terminal node has its own block (dt = 0 by default, benchmark/factory/arm.hpp:89-90)
   if (dt < 0.) dt = 1e-3;
   const bool integ = dt != 0.;
   const double sc = integ ? dt : 1.;  // L* = dt * L*_diff when integrating (euler.hxx:117-121), unscaled otherwise

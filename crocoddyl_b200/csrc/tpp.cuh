@@ -24,6 +24,7 @@
 //   SolverFDDP::forwardPass/(update)expectedImprovement  src/core/solvers/fddp.cpp:107-225
 //   SolverDDP::solve / SolverFDDP::solve  ddp.cpp:41-118, fddp.cpp:19-105
 #pragma once
+#include "boxqp.cuh"
 #include "common.cuh"
 
 namespace cgx {
@@ -42,6 +43,12 @@ struct TppCtx {
   double* trace;  // [cap][NTRACE][Bp] or null
   int trace_cap;
   const double* mparams;  // shared model parameters
+  const double* tparams;  // terminal model's parameters (shooting.hpp:48-63; default = the running block)
+  const double* u_lb;     // [B][U] control limits of the running model (action-base.hxx:117-140)
+  const double* u_ub;
+  const int* has_limits;  // [B]
+  int box;                // 1 = SolverBoxDDP / SolverBoxFDDP
+  double* quu_inv;        // box only: [T][Bp][U*U] (get_Quu_inv, box-ddp.hpp)
   SolverOpts o;
 };
 
@@ -199,7 +206,11 @@ TPP_SWEEP_ATTR double tpp_calc_pass(const TppCtx& c, const M& m, int b, const do
   }
 #pragma unroll
   for (int i = 0; i < U; ++i) u0[i] = 0.;
-  cost += m.calc(rq + L::XU_X, u0, xn);
+  {
+    M mt;  // terminal model (loaded here: its parameters are live only for this node)
+    mt.load(c.tparams);
+    cost += mt.calc(rq + L::XU_X, u0, xn);
+  }
   return cost;
 }
 
@@ -211,7 +222,7 @@ TPP_SWEEP_ATTR double tpp_calc_pass(const TppCtx& c, const M& m, int b, const do
 // because fs[t+1] = xnext(xs[t],us[t]) - xs[t+1] (ddp.cpp:160-171) needs node t's calc; the operations
 // and their order per node are unchanged. Vxx is exactly symmetric after ddp.cpp:235, so only its lower
 // triangle is carried and stored.
-template <class M>
+template <class M, bool BOX = false>
 TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, bool recalc, bool is_feasible,
                                 bool was_feasible, double xreg, double ureg, double& dg_out, double& dq_out,
                                 double& stop_out) {
@@ -234,7 +245,9 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
     double u0[U];
 #pragma unroll
     for (int i = 0; i < U; ++i) u0[i] = 0.;
-    m.calcBoth(rp + L::XU_X, u0, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);
+    M mt;
+    mt.load(c.tparams);
+    mt.calcBoth(rp + L::XU_X, u0, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);
   }
 #pragma unroll
   for (int j = 0; j < N; ++j)
@@ -376,6 +389,36 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
       Qu[j] = Lu[j] + s;
       if (has_ureg) Quu[j + U * j] += ureg;
     }
+    double kkrec[L::R_KK];
+#pragma unroll
+    for (int i = 0; i < L::R_KK; ++i) kkrec[i] = 0.;
+    double* Kg = kkrec + L::KK_K;
+    double* kg = kkrec + L::KK_k;
+    bool boxed = false;
+    if constexpr (BOX) {
+      // SolverBoxDDP/BoxFDDP::computeGains (box-ddp.cpp:46-74): box QP on the control step when the model has control
+      // limits and the candidate is feasible; vanilla gains otherwise
+      boxed = is_feasible && c.has_limits[b] != 0;
+      if (boxed) {
+        double lb[U], ub[U], work[box_gains_work_doubles(U)], qinv[U * U];
+        int iwork[box_gains_work_ints(U)];
+        double kold[L::R_KK];
+        ld_rec<0, L::R_KK / 4>(TPP_REC(c.kk, t, L::R_KK), kold);  // k_[t] of the previous backward pass: the warm start
+#pragma unroll
+        for (int i = 0; i < U; ++i) {
+          lb[i] = c.u_lb[(size_t)b * U + i];
+          ub[i] = c.u_ub[(size_t)b * U + i];
+          kg[i] = kold[L::KK_k + i];
+        }
+        if (box_compute_gains(N, U, Quu, U, Qu, Qxu, N, r + L::XU_U, lb, ub, Kg, U, kg, qinv, c.o, work, iwork)) return 1;
+        if (c.quu_inv) {
+          double* qo = c.quu_inv + ((size_t)t * Bp + b) * (U * U);
+#pragma unroll
+          for (int i = 0; i < U * U; ++i) qo[i] = qinv[i];
+        }
+      }
+    }
+    if (!boxed) {
     // computeGains (ddp.cpp:298-310): unblocked lower LLT, failure iff pivot <= 0
     double Lc[U * U];
 #pragma unroll
@@ -404,11 +447,6 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
       }
     }
     if (fail) return 1;
-    double kkrec[L::R_KK];
-#pragma unroll
-    for (int i = 0; i < L::R_KK; ++i) kkrec[i] = 0.;
-    double* Kg = kkrec + L::KK_K;
-    double* kg = kkrec + L::KK_k;
     // K = Quu^-1 Qxu^T  (columns of K), k = Quu^-1 Qu
 #pragma unroll
     for (int col = 0; col <= N; ++col) {
@@ -437,6 +475,7 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
           kg[i] = rr[i];
       }
     }
+    }  // !boxed
     double Quuk[U];
 #pragma unroll
     for (int i = 0; i < U; ++i) {
@@ -529,7 +568,7 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
 // branch with xs_try[0] = x0) fused with SolverFDDP::expectedImprovement's gap reduction
 // dv = -sum_t fs_t^T Vxx_t (xs_t - xs_try_t) = sum_t w_t^T dx_t (fddp.cpp:107-124).
 // Reads the candidate records XU[cur], writes the trial records XU[cur^1]. Returns 0, or 1 = "forward_error".
-template <class M>
+template <class M, bool BOX = false>
 TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, int cur, double alpha, bool is_feasible,
                                double& cost_try_out, double& dv_out) {
   typedef TppLayout<M> L;
@@ -540,6 +579,18 @@ TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, int cur, doub
   const bool closed = !fddp || is_feasible || (alpha == 1.);
   const bool use_w = fddp && !is_feasible;
   const double am1 = alpha - 1.;
+  // SolverBoxDDP::forwardPass keeps the gap of the TERMINAL node only (box-ddp.cpp:121-125)
+  const bool term_open = BOX && !fddp && !(is_feasible || (alpha == 1.));
+  bool clamp = false;
+  double ulb[U], uub[U];
+  if constexpr (BOX) {
+    clamp = c.has_limits[b] != 0;  // box-ddp.cpp:95-97 / box-fddp.cpp:96-98
+#pragma unroll
+    for (int i = 0; i < U; ++i) {
+      ulb[i] = c.u_lb[(size_t)b * U + i];
+      uub[i] = c.u_ub[(size_t)b * U + i];
+    }
+  }
   const double* __restrict__ xu = c.xu[cur];
   double* __restrict__ xt_ = c.xu[cur ^ 1];
   double cost_try = 0., dv = 0.;
@@ -571,7 +622,7 @@ TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, int cur, doub
     for (int i = 0; i < N; ++i) cw[i] = qw[L::V_W + i];
     if (t < T) fetch(t + 1);
     if (t + TPP_PF_DIST <= T) prefetch(t + TPP_PF_DIST);
-    if (closed) {
+    if (closed && !(term_open && t == T)) {
 #pragma unroll
       for (int i = 0; i < N; ++i) xt[i] = xn[i];
     } else {
@@ -602,6 +653,7 @@ TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, int cur, doub
 #pragma unroll
       for (int j = 0; j < N; ++j) s += ck[L::KK_K + i + U * j] * dx[j];
       u[i] = ca[L::XU_U + i] - ck[L::KK_k + i] * alpha - s;
+      if (BOX && clamp) u[i] = fmin(fmax(u[i], ulb[i]), uub[i]);  // cwiseMax(lb).cwiseMin(ub)
     }
     st_rec<0, SR>(TPP_REC(xt_, t, L::R_XU), o);
     cost_try += m.calc(xt, u, xn);
@@ -617,7 +669,9 @@ TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, int cur, doub
     double u0[U];
 #pragma unroll
     for (int i = 0; i < U; ++i) u0[i] = 0.;
-    cost_try += m.calc(xt, u0, xn);
+    M mt;
+    mt.load(c.tparams);
+    cost_try += mt.calc(xt, u0, xn);
   }
   if (raise_if_nan(cost_try)) return 1;
   cost_try_out = cost_try;
@@ -646,7 +700,7 @@ __device__ inline bool accept_step(const SolverOpts& o, bool fddp, bool is_feasi
 // host compacts the unfinished problems into `list` (tpp_compact_*), so that a launch only spends lanes on OCPs that
 // still iterate: each OCP has its own iteration count, and without compaction one slow lane keeps its whole warp
 // alive (ncu, profiles/README.md: 19 % of the warp slots active at B = 65,536).
-template <class M>
+template <class M, bool BOX = false>
 __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, int is_feasible0, double reginit, int chunk,
                                  int first, const int* __restrict__ list, const int* __restrict__ nactive, int b_lo,
                                  int b_hi) {
@@ -696,7 +750,7 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
     if (recalc) need_gaps = true;
     while (true) {  // computeDirection with regularisation retry (ddp.cpp:55-68)
       if (need_gaps) fsbuf = cur;
-      const int st = tpp_backward(c, m, b, cur, need_gaps, feas, wasfeas, xreg, ureg, dg, dq, stop);
+      const int st = tpp_backward<M, BOX>(c, m, b, cur, need_gaps, feas, wasfeas, xreg, ureg, dg, dq, stop);
       ++nbwd;
       if (st == 0) {
         need_gaps = false;
@@ -720,7 +774,7 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
     for (int a = 0; a < c.o.nalphas; ++a) {
       steplength = c.o.alphas[a];
       double dv = 0.;
-      const int st = tpp_forward(c, m, b, cur, steplength, feas, cost_try, dv);
+      const int st = tpp_forward<M, BOX>(c, m, b, cur, steplength, feas, cost_try, dv);
       ++nfwd;
       if (st) continue;
       dV = cost - cost_try;
@@ -832,7 +886,7 @@ __global__ void __launch_bounds__(1024) tpp_compact_scatter_kernel(const int* __
 // Step-wise kernels (same device functions, state kept in scal/iscal between calls).
 // computeDirection(recalc) (ddp.cpp:120-125): calcDiff (calc + gaps, ddp.cpp:157-178; the step-wise API
 // always runs with iter_ == 0, so problem_->calc is evaluated) + backwardPass.
-template <class M>
+template <class M, bool BOX = false>
 __global__ void __launch_bounds__(64) tpp_direction_kernel(const __grid_constant__ TppCtx c, int recalc) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= c.B) return;
@@ -846,7 +900,7 @@ __global__ void __launch_bounds__(64) tpp_direction_kernel(const __grid_constant
     TPP_I(I_FSBUF) = cur;
   }
   double dg = 0., dq = 0., stop = 0.;
-  const int st = tpp_backward(c, m, b, cur, recalc != 0, feas, wasfeas, TPP_S(S_XREG), TPP_S(S_UREG), dg, dq, stop);
+  const int st = tpp_backward<M, BOX>(c, m, b, cur, recalc != 0, feas, wasfeas, TPP_S(S_XREG), TPP_S(S_UREG), dg, dq, stop);
   TPP_I(I_BSTATUS) = st;
   if (st == 0) {
     TPP_S(S_DG) = dg;
@@ -860,7 +914,7 @@ __global__ void __launch_bounds__(64) tpp_direction_kernel(const __grid_constant
 }
 
 // tryStep(alpha) (ddp.cpp:127-130)
-template <class M>
+template <class M, bool BOX = false>
 __global__ void __launch_bounds__(64) tpp_trystep_kernel(const __grid_constant__ TppCtx c, double alpha) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= c.B) return;
@@ -870,7 +924,7 @@ __global__ void __launch_bounds__(64) tpp_trystep_kernel(const __grid_constant__
   const int cur = TPP_I(I_CUR);
   const bool feas = TPP_I(I_FEAS) != 0;
   double cost_try = 0., dv = 0.;
-  const int st = tpp_forward(c, m, b, cur, alpha, feas, cost_try, dv);
+  const int st = tpp_forward<M, BOX>(c, m, b, cur, alpha, feas, cost_try, dv);
   TPP_I(I_FSTATUS) = st;
   if (st == 0) {
     TPP_S(S_COST_TRY) = cost_try;
@@ -896,7 +950,7 @@ __global__ void tpp_node_data_kernel(TppCtx c, const double* __restrict__ xs, co
   const int t = blockIdx.y;
   if (b >= c.B) return;
   M m;
-  m.load(c.mparams);
+  m.load(t < T ? c.mparams : c.tparams);
   double x[N], u[U], xn[N], fx[N * N], fu[N * U], lx[N], lu[U], lxx[N * N], lxu[N * U], luu[U * U];
   const size_t node = (size_t)b * (T + 1) + t;
 #pragma unroll

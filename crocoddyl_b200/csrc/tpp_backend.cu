@@ -9,6 +9,17 @@ namespace cgx {
 
 namespace {
 
+// launch kernel<M, BOX> with BOX = c.box: the control-limited solvers are separate instantiations, so the register
+// budget and the code of the unconstrained solve kernel are untouched by them
+#define CGX_UNPAREN(...) __VA_ARGS__
+#define TPP_LAUNCH_BOX(kernel, cfg, ...)                        \
+  do {                                                          \
+    if (c.box)                                                  \
+      kernel<M, true><<<CGX_UNPAREN cfg>>>(__VA_ARGS__);        \
+    else                                                        \
+      kernel<M, false><<<CGX_UNPAREN cfg>>>(__VA_ARGS__);       \
+  } while (0)
+
 template <class M>
 struct TppBackend : Backend {
   static constexpr int N = M::NX, U = M::NU;
@@ -25,10 +36,15 @@ struct TppBackend : Backend {
     c.B = p->B;
     c.Bp = ((p->B + 63) / 64) * 64;
     c.T = p->T;
-    c.fddp = sk == 1;
+    c.fddp = sk == 1 || sk == 3;  // SolverFDDP / SolverBoxFDDP
+    c.box = sk >= 2;              // SolverBoxDDP / SolverBoxFDDP
     CGX_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     for (int i = 0; i < 4; ++i) CGX_CUDA(cudaEventCreate(&ev[i]));
     c.mparams = p->d_params;
+    c.tparams = p->d_tparams;
+    c.u_lb = p->d_ulb;
+    c.u_ub = p->d_uub;
+    c.has_limits = p->d_haslim;
     c.x0 = alloc((size_t)N * c.Bp);
     x0_changed();
   }
@@ -101,6 +117,7 @@ struct TppBackend : Backend {
       solver_allocated = true;
     }
     if (full && !c.q) c.q = alloc(T * Bp * L::R_Q);
+    if (c.box && !c.quu_inv) c.quu_inv = alloc(T * Bp * U * U);
     c.full = full;
     if (trace_on && (!c.trace || c.trace_cap != trace_cap)) {
       release(c.trace);
@@ -187,7 +204,7 @@ struct TppBackend : Backend {
       gather(d_xs + ox, fx.fm, c.xu[0], c.xu[0], nullptr, 0, b0, nb, 1, st);
       gather(d_us + ou, fu.fm, c.xu[0], c.xu[0], nullptr, 0, b0, nb, 1, st);
       if (ptrace) CGX_CUDA(cudaEventRecord(ptime[k][0], st));
-      tpp_solve_kernel<M><<<(nb + 63) / 64, TPP_BLOCK, 0, st>>>(c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr,
+      TPP_LAUNCH_BOX(tpp_solve_kernel, ((nb + 63) / 64, TPP_BLOCK, 0, st), c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr,
                                                                b0, b0 + nb);
       ++last_launches;
       if (ptrace) CGX_CUDA(cudaEventRecord(ptime[k][1], st));
@@ -233,7 +250,7 @@ struct TppBackend : Backend {
     const int chunk = chunk_iters();
     CGX_CUDA(cudaEventRecord(ev[1], stream));
     if (chunk <= 0 || maxiter <= chunk) {
-      tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr, 0, c.B);
+      TPP_LAUNCH_BOX(tpp_solve_kernel, (nblocks(), TPP_BLOCK, 0, stream), c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr, 0, c.B);
       ++last_launches;
     } else {
       const int cblocks = (c.B + 1023) / 1024;
@@ -244,12 +261,12 @@ struct TppBackend : Backend {
       int* d_counts = d_list + c.Bp;
       int* d_nactive = d_counts + cblocks;
       const int* fin = c.iscal + (size_t)I_FINISHED * c.Bp;
-      tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit, chunk, 1, nullptr, nullptr, 0, c.B);
+      TPP_LAUNCH_BOX(tpp_solve_kernel, (nblocks(), TPP_BLOCK, 0, stream), c, maxiter, is_feasible, reginit, chunk, 1, nullptr, nullptr, 0, c.B);
       ++last_launches;
       for (int done = chunk; done < maxiter; done += chunk) {
         tpp_compact_count_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts);
         tpp_compact_scatter_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts, d_list, d_nactive);
-        tpp_solve_kernel<M><<<nblocks(), TPP_BLOCK, 0, stream>>>(c, maxiter, is_feasible, reginit, chunk, 0, d_list, d_nactive, 0, c.B);
+        TPP_LAUNCH_BOX(tpp_solve_kernel, (nblocks(), TPP_BLOCK, 0, stream), c, maxiter, is_feasible, reginit, chunk, 0, d_list, d_nactive, 0, c.B);
         last_launches += 3;
       }
     }
@@ -259,7 +276,7 @@ struct TppBackend : Backend {
   void compute_direction(int recalc) override {
     c.o = o;
     CGX_CUDA(cudaEventRecord(ev[1], stream));
-    tpp_direction_kernel<M><<<nblocks(), 64, 0, stream>>>(c, recalc);
+    TPP_LAUNCH_BOX(tpp_direction_kernel, (nblocks(), 64, 0, stream), c, recalc);
     CGX_CUDA(cudaEventRecord(ev[2], stream));
     ++last_launches;
     CGX_CUDA(cudaGetLastError());
@@ -267,7 +284,7 @@ struct TppBackend : Backend {
   void try_step(double alpha) override {
     c.o = o;
     CGX_CUDA(cudaEventRecord(ev[1], stream));
-    tpp_trystep_kernel<M><<<nblocks(), 64, 0, stream>>>(c, alpha);
+    TPP_LAUNCH_BOX(tpp_trystep_kernel, (nblocks(), 64, 0, stream), c, alpha);
     CGX_CUDA(cudaEventRecord(ev[2], stream));
     ++last_launches;
     CGX_CUDA(cudaGetLastError());
@@ -307,6 +324,12 @@ struct TppBackend : Backend {
       f.a = f.b = c.kk;
       if (n == "K") seq(L::R_KK, U * N, T, L::KK_K);
       else seq(L::R_KK, U, T, L::KK_k);
+      return f;
+    }
+    if (n == "Quu_inv") {  // SolverBoxDDP::get_Quu_inv (box-ddp.hpp)
+      if (!c.quu_inv) throw Unsupported("Quu_inv is kept by the box solvers only");
+      f.a = f.b = c.quu_inv;
+      seq(U * U, U * U, T, 0);
       return f;
     }
     if (n == "Vx" || n == "Vxx") {

@@ -54,8 +54,10 @@ enum cgx_model_kind {
                              include/crocoddyl/multibody/actions/free-fwddyn.hxx:44-169 */
 };
 enum cgx_solver_kind {
-  CGX_SOLVER_DDP = 0, /* src/core/solvers/ddp.cpp */
-  CGX_SOLVER_FDDP = 1 /* src/core/solvers/fddp.cpp */
+  CGX_SOLVER_DDP = 0,     /* src/core/solvers/ddp.cpp */
+  CGX_SOLVER_FDDP = 1,    /* src/core/solvers/fddp.cpp */
+  CGX_SOLVER_BOXDDP = 2,  /* src/core/solvers/box-ddp.cpp  (control-limited, BoxQP in computeGains, clamp in forwardPass) */
+  CGX_SOLVER_BOXFDDP = 3  /* src/core/solvers/box-fddp.cpp */
 };
 
 CGX_API const char* cgx_last_error(void);
@@ -82,6 +84,18 @@ CGX_API const char* cgx_version(void);
 CGX_API int cgx_problem_create(cgx_problem_t* out, int kind, int B, int T, int nx, int nu, const double* params,
                        long nparams, int per_problem_params, const double* x0s);
 CGX_API int cgx_problem_destroy(cgx_problem_t p);
+/* A terminal model that differs from the running model: ShootingProblem(x0, running_models, terminal_model)
+ * (shooting.hpp:48-63) with terminal_model != running_models[0], as examples/arm_manipulation.py:41-63 (terminal cost =
+ * gripperPose only). tparams has the layout and size of the running block (same kind, nx; per_problem_params as given at
+ * creation). Without this call the terminal node uses the running block — for CGX_MODEL_ARM with dt = 0, the model of
+ * benchmark/factory/arm.hpp:89-90. The terminal block's dt is used as given (Euler with dt = 0 for a terminal knot). */
+CGX_API int cgx_problem_set_terminal_params(cgx_problem_t p, const double* tparams, long nparams);
+CGX_API int cgx_problem_get_terminal_params(cgx_problem_t p, double* tparams);
+/* ActionModelAbstract::set_u_lb / set_u_ub of the running model (action-base.hxx:117-140): lb, ub = [nu] shared by the
+ * batch (per_problem == 0) or [B][nu]; +-INFINITY = unbounded. has_control_limits follows the reference rule (some finite
+ * entry in lb AND some finite entry in ub). Read by CGX_SOLVER_BOXDDP / CGX_SOLVER_BOXFDDP. */
+CGX_API int cgx_problem_set_u_bounds(cgx_problem_t p, const double* lb, const double* ub, int per_problem);
+CGX_API int cgx_problem_get_u_bounds(cgx_problem_t p, double* lb, double* ub, int* per_problem, int* has_control_limits);
 CGX_API int cgx_problem_set_x0(cgx_problem_t p, const double* x0s); /* ShootingProblem::set_x0 shooting.hxx:393-400 */
 CGX_API int cgx_problem_get_x0(cgx_problem_t p, double* x0s);       /* get_x0 shooting.hxx:325-328 */
 /* get_T / get_nx / get_ndx / get_nu_max (shooting.hxx:319-322, 367-390) and the batch size */
@@ -163,7 +177,8 @@ CGX_API int cgx_solver_expected_improvement(cgx_solver_t s, double* d);
 CGX_API int cgx_solver_stopping_criteria(cgx_solver_t s, double* stop);
 
 /* accessors. name in {"xs","us","xs_try","us_try","fs","K","k","Vx","Vxx","Qxx","Qxu","Quu","Qx","Qu"}
- * (solver-base.hpp:162-167, ddp.hpp:191-236). t == T is valid for xs, xs_try, fs, Vx, Vxx.
+ * (solver-base.hpp:162-167, ddp.hpp:191-236) and, for the box solvers, "Quu_inv" (box-ddp.hpp get_Quu_inv).
+ * t == T is valid for xs, xs_try, fs, Vx, Vxx.
  * cgx_solver_get: one node of one problem, returns the number of doubles written.
  * cgx_solver_get_all: all nodes of all problems, out = [B][nt][size]. */
 CGX_API int cgx_solver_get(cgx_solver_t s, const char* name, int b, int t, double* out);

@@ -74,8 +74,17 @@ extern "C" {
 //   UNICYCLE : [dt, w_x, w_u]
 //   ARM      : see arm.hpp (arm_param_count)
 // per_problem_params != 0: params holds B consecutive blocks; else one shared block.
+// tparams (may be NULL): parameter block(s) of the TERMINAL model, same layout / count / per-problem-ness as params
+// (ShootingProblem(x0, running_models, terminal_model) with a terminal model of its own, shooting.hpp:48-63). NULL: the
+// running model is aliased into the terminal node (arm: the running differential model with dt = 0, arm.hpp:89-90).
+void* orc_batch_create2(int kind, int solver_kind, int B, int T, int nx, int nu, const double* params, long nparams,
+                        int per_problem_params, const double* x0s, const double* tparams);
 void* orc_batch_create(int kind, int solver_kind, int B, int T, int nx, int nu, const double* params, long nparams,
                        int per_problem_params, const double* x0s) {
+  return orc_batch_create2(kind, solver_kind, B, T, nx, nu, params, nparams, per_problem_params, x0s, nullptr);
+}
+void* orc_batch_create2(int kind, int solver_kind, int B, int T, int nx, int nu, const double* params, long nparams,
+                        int per_problem_params, const double* x0s, const double* tparams) {
   Batch* bt = new Batch();
   bt->kind = kind;
   bt->solver_kind = solver_kind;
@@ -93,6 +102,7 @@ void* orc_batch_create(int kind, int solver_kind, int B, int T, int nx, int nu, 
         if (kind == KIND_LQR) {
           if ((size_t)nparams != lqr_param_count(nx, nu)) throw std::invalid_argument("LQR params: wrong count");
           run = term = make_lqr(nx, nu, p);
+          if (tparams) term = make_lqr(nx, nu, tparams + (per_problem_params ? (size_t)b * nparams : 0));
         } else if (kind == KIND_UNICYCLE) {
           if (nparams != 3) throw std::invalid_argument("unicycle params: wrong count");
           std::shared_ptr<ActionModelUnicycle> u = std::make_shared<ActionModelUnicycle>();
@@ -100,8 +110,20 @@ void* orc_batch_create(int kind, int solver_kind, int B, int T, int nx, int nu, 
           u->cost_weights[0] = p[1];
           u->cost_weights[1] = p[2];
           run = term = u;
+          if (tparams) {
+            const double* q = tparams + (per_problem_params ? (size_t)b * nparams : 0);
+            std::shared_ptr<ActionModelUnicycle> ut = std::make_shared<ActionModelUnicycle>();
+            ut->dt = q[0];
+            ut->cost_weights[0] = q[1];
+            ut->cost_weights[1] = q[2];
+            term = ut;
+          }
         } else if (kind == KIND_ARM) {
           make_arm_models(p, nparams, nx, nu, run, term);
+          if (tparams) {  // the terminal block is used as given (its own dt, weights, frame reference)
+            std::shared_ptr<ActionModel> unused;
+            make_arm_models(tparams + (per_problem_params ? (size_t)b * nparams : 0), nparams, nx, nu, term, unused);
+          }
         } else {
           throw std::invalid_argument("unknown model kind");
         }

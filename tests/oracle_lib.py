@@ -30,6 +30,8 @@ def load(fast=False):
     lib = C.CDLL(path)
     lib.orc_batch_create.restype = C.c_void_p
     lib.orc_batch_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _dp, C.c_long, C.c_int, _dp]
+    lib.orc_batch_create2.restype = C.c_void_p
+    lib.orc_batch_create2.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _dp, C.c_long, C.c_int, _dp, _dp]
     lib.orc_batch_destroy.argtypes = [C.c_void_p]
     lib.orc_batch_set.argtypes = [C.c_void_p, C.c_char_p, C.c_double]
     lib.orc_batch_set_alphas.argtypes = [C.c_void_p, _dp, C.c_int]
@@ -55,18 +57,21 @@ def load(fast=False):
 class OracleBatch:
     """A batch of B independent OCPs solved by the CPU oracle (one solver object per problem)."""
 
-    def __init__(self, kind, solver, T, nx, nu, params, x0s, fast=False):
+    def __init__(self, kind, solver, T, nx, nu, params, x0s, fast=False, tparams=None):
         self.lib = load(fast)
         x0s = np.ascontiguousarray(x0s, dtype=np.float64).reshape(-1, nx)
         params = np.ascontiguousarray(params, dtype=np.float64)
         self.B, self.T, self.nx, self.nu = x0s.shape[0], T, nx, nu
         per = params.ndim == 2
         nparams = params.shape[-1]
-        self.h = self.lib.orc_batch_create(KIND[kind], SOLVER[solver], self.B, T, nx, nu, _p(params), nparams,
-                                           int(per), _p(x0s))
+        if tparams is not None:
+            tparams = np.ascontiguousarray(tparams, dtype=np.float64)
+            assert tparams.shape == params.shape, "terminal block: same layout and per-problem-ness as the running one"
+        self.h = self.lib.orc_batch_create2(KIND[kind], SOLVER[solver], self.B, T, nx, nu, _p(params), nparams,
+                                            int(per), _p(x0s), _p(tparams))
         if not self.h:
             raise RuntimeError("orc_batch_create failed")
-        self._keep = (params, x0s)
+        self._keep = (params, x0s, tparams)
 
     def __del__(self):
         if getattr(self, "h", None):

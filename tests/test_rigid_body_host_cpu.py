@@ -63,10 +63,12 @@ def test_node_calc_and_calcdiff_match_oracle(host_rb, kind, nv):
     for t in range(T + 1):
         term = t == T
         u = None if term else us[t]
-        got = _eval(host_rb, nv, "c", params, term, xs[t], u)
+        # the terminal node is evaluated on its own parameter block (the product's default: the running block with dt = 0)
+        pt = model.terminal_model.params() if term else params
+        got = _eval(host_rb, nv, "c", pt, term, xs[t], u)
         np.testing.assert_allclose(got[0], ob.get("node_cost", 0, t)[0], rtol=1e-12, atol=1e-14)
         np.testing.assert_allclose(got[1:1 + n], ob.get("xnext", 0, t), rtol=1e-12, atol=1e-13)
-        d = _eval(host_rb, nv, "d", params, term, xs[t], u)
+        d = _eval(host_rb, nv, "d", pt, term, xs[t], u)
         o = 0
         for name, shp in [("Fx", (n, n)), ("Fu", (n, nv)), ("Lx", (n,)), ("Lu", (nv,)), ("Lxx", (n, n)), ("Luu", (nv, nv))]:
             sz = int(np.prod(shp))

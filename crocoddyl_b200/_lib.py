@@ -70,6 +70,7 @@ SIGNATURES = {
     "cgx_solver_set_xs": (C.c_int, [_vp, _dp]),
     "cgx_solver_set_us": (C.c_int, [_vp, _dp]),
     "cgx_solver_get_scalars": (C.c_int, [_vp, _dp]),
+    "cgx_solver_get_scalars_row": (C.c_int, [_vp, C.c_int, _dp]),
     "cgx_solver_get_trace": (C.c_int, [_vp, C.c_int, _dp, C.c_int]),
     "cgx_solver_set_callback": (C.c_int, [_vp, CALLBACK, _vp]),
     "cgx_solver_last_timing": (C.c_int, [_vp, _dp, _ip]),

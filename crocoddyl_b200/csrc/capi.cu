@@ -17,6 +17,7 @@ struct cgx_problem_s {
   double* d_tmp_xs = nullptr;
   double* d_tmp_us = nullptr;
   double* d_tmp_cost = nullptr;
+  double* d_tmp_data = nullptr;  // one ActionData field of one node (largest: ndx x ndx)
 };
 
 // page-locked host block for the per-problem scalar record: the D2H copy of [B][17] doubles runs at PCIe rate instead
@@ -242,6 +243,7 @@ int cgx_problem_destroy(cgx_problem_t p) {
   if (p->d_tmp_xs) cudaFree(p->d_tmp_xs);
   if (p->d_tmp_us) cudaFree(p->d_tmp_us);
   if (p->d_tmp_cost) cudaFree(p->d_tmp_cost);
+  if (p->d_tmp_data) cudaFree(p->d_tmp_data);
   delete p;
   return CGX_OK;
 }
@@ -324,6 +326,8 @@ static void problem_backend(cgx_problem_s* p) {
     p->d_tmp_xs = dalloc<double>(B * (T + 1) * p->d.nx);
     p->d_tmp_us = dalloc<double>(B * T * (p->d.nu ? p->d.nu : 1));
     p->d_tmp_cost = dalloc<double>(B);
+    const size_t n = p->d.nx, m = p->d.nu ? p->d.nu : 1;
+    p->d_tmp_data = dalloc<double>(n * n + n * m + m * m);
   }
 }
 
@@ -395,8 +399,8 @@ int cgx_problem_get_data(cgx_problem_t p, const char* field, int b, int t, doubl
   problem_backend(p);
   Backend* be = p->pb;
   FieldInfo fi = be->data_info(field);
-  be->export_data(field, b, t, p->d_tmp_xs);
-  CGX_CUDA(cudaMemcpyAsync(out, p->d_tmp_xs, fi.size * sizeof(double), cudaMemcpyDeviceToHost, be->stream));
+  be->export_data(field, b, t, p->d_tmp_data);
+  CGX_CUDA(cudaMemcpyAsync(out, p->d_tmp_data, fi.size * sizeof(double), cudaMemcpyDeviceToHost, be->stream));
   CGX_CUDA(cudaStreamSynchronize(be->stream));
   return fi.size;
   CGX_CATCH
@@ -794,6 +798,17 @@ int cgx_solver_get_scalars(cgx_solver_t s, double* out) {
   if (!s || !out) throw InvalidArg("Invalid argument: NULL");
   fetch_scalars(s);
   std::memcpy(out, s->h_scal.data(), s->h_scal.size() * sizeof(double));
+  return CGX_OK;
+  CGX_CATCH
+}
+
+int cgx_solver_get_scalars_row(cgx_solver_t s, int b, double* out) {
+  CGX_TRY
+  if (!s || !out) throw InvalidArg("Invalid argument: NULL");
+  if (b < 0 || b >= s->p->d.B) throw InvalidArg("Invalid argument: b out of range");
+  s->be->export_scalars(s->d_scal);
+  CGX_CUDA(cudaMemcpyAsync(out, s->d_scal + (size_t)b * 17, 17 * sizeof(double), cudaMemcpyDeviceToHost, s->be->stream));
+  CGX_CUDA(cudaStreamSynchronize(s->be->stream));
   return CGX_OK;
   CGX_CATCH
 }

@@ -466,10 +466,10 @@ __device__ double cta_calcdiff(const CtaCtx& c, const M& mod, CtaSmem& sm, int b
 // stoppingCriteria (ddp.cpp:132-142). Returns 0 or 1 ("backward_error") to all threads; dg,dq,stop valid on
 // every thread.
 template <class M>
-__device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, bool is_feasible, double xreg,
+__device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, int cur, bool is_feasible, double xreg,
                             double ureg, double& dg_out, double& dq_out, double& stop_out) {
 #ifndef CGX_NO_SMALL_BACKWARD
-  if (cta_is_small(c.n, c.m)) return cta_backward_warp<M::kN, M::kM>(c, mod, b, is_feasible, xreg, ureg, dg_out, dq_out, stop_out);
+  if (cta_is_small(c.n, c.m)) return cta_backward_warp<M::kN, M::kM>(c, mod, b, cur, is_feasible, xreg, ureg, dg_out, dq_out, stop_out);
 #endif
   const int T = c.T, n = c.n, m = c.m, ldn = sm.ldn, ldm = sm.ldm;
   const int tid = threadIdx.x, P = blockDim.x;
@@ -557,7 +557,7 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, b
     const bool boxed = c.box && is_feasible && c.has_limits[b] != 0;
     if (boxed) {
       if (tid == 0) {
-        const double* u_t = c.us[CTA_I_(c, b, I_CUR)] + rnode * m;
+        const double* u_t = c.us[cur] + rnode * m;  // us_[t] of the candidate
         for (int i = 0; i < m; ++i) sm.kg[i] = c.k[rnode * m + i];  // k_[t] of the previous backward pass (warm start)
         *sm.flag = box_compute_gains(n, m, sm.Quu, ldm, sm.Qu, sm.Qxu, ldn, u_t, c.u_lb + (size_t)b * m,
                                      c.u_ub + (size_t)b * m, sm.Kg, ldm, sm.kg, c.Quu_inv + rnode * m * m, c.o,
@@ -869,7 +869,7 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_solve_kerne
     int retries = 0;
     while (true) {  // computeDirection(recalcDiff) with regularisation retry (ddp.cpp:55-68)
       if (recalc) cost = cta_calcdiff(c, mod, sm, b, cur, iter == 0, feas, wasfeas);
-      const int st = cta_backward(c, mod, sm, b, feas, xreg, ureg, dg, dq, stop);
+      const int st = cta_backward(c, mod, sm, b, cur, feas, xreg, ureg, dg, dq, stop);
       ++nbwd;
       if (st == 0) break;
       recalc = false;
@@ -1031,7 +1031,7 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kDirMinBlocks) cta_phase_di
   __syncthreads();
   double cost = 0.;
   if (recalc) cost = cta_calcdiff<M, M::kNodeKernel>(c, mod, sm, b, cur, iter == 0, feas, wasfeas);
-  const int st = cta_backward(c, mod, sm, b, feas, xreg, ureg, dg, dq, stop);
+  const int st = cta_backward(c, mod, sm, b, cur, feas, xreg, ureg, dg, dq, stop);
   if (threadIdx.x != 0) return;
   if (recalc) CTA_S(S_COST) = cost;
   ++CTA_I(I_NBWD);
@@ -1254,7 +1254,7 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_direction_k
   }
   if (what == 0) return;
   double dg = 0., dq = 0., stop = 0.;
-  const int st = cta_backward(c, mod, sm, b, feas, CTA_S(S_XREG), CTA_S(S_UREG), dg, dq, stop);
+  const int st = cta_backward(c, mod, sm, b, cur, feas, CTA_S(S_XREG), CTA_S(S_UREG), dg, dq, stop);
   if (threadIdx.x == 0) {
     CTA_I(I_BSTATUS) = st;
     ++CTA_I(I_NBWD);

@@ -97,7 +97,7 @@ __device__ __forceinline__ void warp_st_matrix(double* gdst, const double* src, 
 // phase in registers and advances all of them together along k, so the shared-memory loads of one k-step are
 // independent and pipelined (a single accumulator per lane serialises LDS -> DFMA: measured 20 us per node).
 template <int KN, int KM, class M>
-__device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, bool is_feasible, double xreg, double ureg,
+__device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, int cur, bool is_feasible, double xreg, double ureg,
                                  double& dg_out, double& dq_out, double& stop_out) {
   extern __shared__ double cta_smem_raw[];
   double* S = cta_smem_raw;
@@ -301,7 +301,7 @@ __device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, bool is_f
       const bool boxed = c.box && is_feasible && c.has_limits[b] != 0;
       if (boxed) {
         if (lane == 0) {
-          const double* u_t = c.us[CTA_I_(c, b, I_CUR)] + rnode * m;
+          const double* u_t = c.us[cur] + rnode * m;  // us_[t] of the candidate
           for (int i = 0; i < m; ++i) kg[i] = c.k[rnode * m + i];  // k_[t] of the previous backward pass (warm start)
           *flag = box_compute_gains(n, m, Quu, ldm, Qu, Qxu, ldn, u_t, c.u_lb + (size_t)b * m, c.u_ub + (size_t)b * m, Kg,
                                     ldm, kg, c.Quu_inv + rnode * m * m, c.o,

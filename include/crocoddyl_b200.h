@@ -193,6 +193,8 @@ CGX_API int cgx_solver_set_us(cgx_solver_t s, const double* us);
  *  (the sweep counts give the algorithmic HBM bytes of a solve) */
 #define CGX_NSCALARS 17
 CGX_API int cgx_solver_get_scalars(cgx_solver_t s, double* out);
+/* the same for ONE problem: out = [CGX_NSCALARS] (the per-problem getters get_cost(), get_stop(), ... of the facade) */
+CGX_API int cgx_solver_get_scalars_row(cgx_solver_t s, int b, double* out);
 
 /* one row per iteration, out = [n][CGX_NTRACE]:
  *  0 iter 1 cost 2 stop 3 d0 4 d1 5 xreg 6 ureg 7 steplength 8 is_feasible 9 dV 10 dVexp

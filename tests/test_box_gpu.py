@@ -33,7 +33,8 @@ def _uni(B, seed):
 
 
 def _arm(B, seed, nv=7):
-    mod = cb.ArmActionModel(cb.synthetic_arm(nv), 1e-3)
+    # a horizon long enough (20 x 10 ms) and a goal cost strong enough for the torques to reach their limits
+    mod = cb.ArmActionModel(cb.synthetic_arm(nv), 1e-2, w_gripperPose=10., w_xReg=1e-3, w_uReg=1e-4)
     rng = np.random.default_rng(seed)
     return mod, np.concatenate([rng.uniform(-1, 1, (B, nv)), np.zeros((B, nv))], 1)
 
@@ -43,7 +44,7 @@ CASES = {
     "unicycle": ("unicycle", lambda: _uni(48, 1), 30, 0.8, 1e-9, 100),
     "lqr_small": ("lqr", lambda: _lqr(9, 6, 3, 2), 15, 0.3, 1e-9, 50),
     "lqr_large": ("lqr", lambda: _lqr(5, 20, 6, 3), 10, 0.3, 1e-9, 50),
-    "arm": ("arm", lambda: _arm(6, 4), 12, None, 0.1, 40),
+    "arm": ("arm", lambda: _arm(6, 4), 20, None, 0.1, 60),
 }
 
 
@@ -56,7 +57,7 @@ def _setup(name, kind):
     if family == "arm":
         u0 = problem.quasiStatic(x0)
         us = np.repeat(u0[:, None, :], T, 1)
-        lb, ub = u0.min(0) - 2.0, u0.max(0) + 2.0  # tight around the gravity torques: active during the solve
+        lb, ub = u0.min(0) - 5.0, u0.max(0) + 5.0  # around the gravity torques: ~3/4 of the controls end on a limit
     else:
         us = np.zeros((B, T, mod.nu))
         lb, ub = -lim * np.ones(mod.nu), lim * np.ones(mod.nu)
@@ -64,6 +65,10 @@ def _setup(name, kind):
     solver = (cb.SolverBoxFDDP if kind == "boxfddp" else cb.SolverBoxDDP)(problem)
     ob = ol.OracleBatch(family, kind, T, mod.nx, mod.nu, mod.params(), x0)
     ob.set_u_bounds(lb, ub)
+    assert solver.th_stop == 5e-5  # box-ddp.cpp:29
+    if family == "arm":  # the default tolerance of the box solvers stops this case after two iterations
+        solver.th_stop = 1e-7
+        ob.set("th_stop", 1e-7)
     xs = np.repeat(x0[:, None, :], T + 1, 1)
     return problem, solver, ob, xs, us, lb, ub, reginit, maxiter
 
@@ -91,7 +96,7 @@ def test_stepwise_box_gains_and_clamped_rollout(name, kind):
             np.testing.assert_allclose(solver.get(f), ob.get_all(f), err_msg="%s pass %d" % (f, s), **TOL)
         assert (solver.get("Qu") == 0.).any(), "no clamped control: the case does not exercise the box QP"
         Qi = solver.get("Quu_inv")
-        assert np.all(Qi == np.transpose(Qi, (0, 1, 3, 2)))
+        np.testing.assert_allclose(Qi, np.transpose(Qi, (0, 1, 3, 2)), rtol=1e-9, atol=1e-12)  # inverse of the free block
     np.testing.assert_allclose(solver.stoppingCriteria(), ob.expected_improvement()[1], **TOL)
     for alpha in (1.0, 0.25):
         dV = solver.tryStep(alpha)
@@ -115,7 +120,6 @@ def test_solve_box_same_sequence_as_oracle(name, kind):
     conv = solver.solve(xs, us, maxiter, False, reginit)
     ob.solve(xs, us, maxiter, False, reginit)
     so, sg = ob.scalars(), solver.scalars()
-    assert solver.th_stop == 5e-5  # box-ddp.cpp:29
     same = so["n_records"] == sg["n_records"]
     assert same.mean() >= 0.9, (so["n_records"], sg["n_records"])
     assert np.array_equal(so["converged"].astype(bool)[same], np.atleast_1d(conv)[same])

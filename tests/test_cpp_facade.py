@@ -57,3 +57,27 @@ def test_facade_solve_matches_oracle(kind, T):
     np.testing.assert_allclose(vals["us"], ob.get_all("us").ravel(), rtol=1e-9, atol=1e-9)
     np.testing.assert_allclose(vals["K0"], ob.get("K", 0, 0).ravel(order="F"), rtol=1e-9, atol=1e-9)
     assert "Warm start state has wrong dimension" in lines[4]
+    # node plugin interface: model->calc / calcDiff on one node against the oracle's node model
+    x = 0.3 + 0.1 * np.arange(nx)
+    u = -0.2 + 0.5 * np.arange(nu)
+    one = ol.OracleBatch(kind, "ddp", 1, nx, nu, params, x[None])
+    one.set_candidate(np.stack([x, x])[None], u[None, None], False)
+    one.calc()
+    one.calcdiff()
+    node = {ln.split()[0]: np.array([float(v) for v in ln.split()[1:]]) for ln in lines[6:9]}
+    np.testing.assert_allclose(float(lines[5].split()[2]), one.get("node_cost", 0, 0)[0], rtol=1e-12)
+    np.testing.assert_allclose(node["node_xnext"], one.get("xnext", 0, 0), rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(node["node_Fx"], one.get("Fx", 0, 0).ravel(order="F"), rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(node["node_Lu"], one.get("Lu", 0, 0), rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(float(lines[9].split()[2]), one.get("node_cost", 0, 1)[0], rtol=1e-12)
+    # control-limited solve through SolverBoxFDDP
+    bo = ol.OracleBatch(kind, "boxfddp", T, nx, nu, params, x0)
+    bo.set_u_bounds(-0.4 * np.ones(nu), 0.4 * np.ones(nu))
+    bo.solve(np.repeat(x0[:, None, :], T + 1, 1), np.zeros((1, T, nu)), 100, False, 1e-9)
+    bh = lines[10].split()
+    assert bh[0] == "box" and float(bh[8]) == 5e-5
+    assert int(bh[2]) == int(bo.scalars()["converged"][0]) and int(bh[4]) == int(bo.scalars()["iter"][0])
+    np.testing.assert_allclose(float(bh[6]), bo.scalars()["cost"][0], rtol=1e-9)
+    bu = np.array([float(v) for v in lines[11].split()[1:]])
+    assert np.all(np.abs(bu) <= 0.4 + 1e-15)
+    np.testing.assert_allclose(bu, bo.get_all("us").ravel(), rtol=1e-7, atol=1e-8)

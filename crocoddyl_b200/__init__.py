@@ -196,14 +196,36 @@ class ShootingProblem(object):
 
 
 class CallbackLogger(object):
-    """Per-iteration log with the schema of the reference's CallbackLogger
-    (bindings/python/crocoddyl/__init__.py:356-381), one list per problem."""
+    """CallbackLogger of the reference (bindings/python/crocoddyl/__init__.py:356-381): xs, us, fs, steps, iters, costs,
+    u_regs, x_regs, stops, grads — for ONE problem of the batch (`problem`, default 0), filled from the device's
+    per-iteration trace after the solve. steps / iters / costs / u_regs / x_regs / stops / grads hold one entry per
+    iteration exactly like the reference's; xs and us are the solver's final iterate (what the reference's last call
+    leaves there). The device loop does not return to the host between iterations, so `fs` holds the gaps of the LAST
+    computeDirection only (one entry) instead of one entry per iteration. `records` keeps the raw trace rows."""
 
-    def __init__(self):
+    def __init__(self, problem=0):
+        self.problem = problem
+        self.xs, self.us, self.fs = [], [], []
+        self.steps, self.iters, self.costs, self.u_regs, self.x_regs, self.stops, self.grads = [], [], [], [], [], [], []
         self.records = []
 
     def __call__(self, rec):
+        if rec["problem"] != self.problem:
+            return
         self.records.append(dict(rec))
+        self.steps.append(rec["steplength"])
+        self.iters.append(rec["iter"])
+        self.costs.append(rec["cost"])
+        self.u_regs.append(rec["ureg"])
+        self.x_regs.append(rec["xreg"])
+        self.stops.append(rec["stop"])
+        self.grads.append(-rec["d1"])  # -expectedImprovement()[1]
+
+    def finalize(self, solver):
+        b = self.problem
+        self.xs = list(solver.get("xs")[b])
+        self.us = list(solver.get("us")[b])
+        self.fs = [list(solver.get("fs")[b])]
 
 
 class CallbackVerbose(object):
@@ -267,6 +289,7 @@ class SolverDDP(object):
         check(lib().cgx_solver_solve(self._h, dptr(xs), dptr(us), int(maxiter), int(bool(isFeasible)), reg,
                                      conv.ctypes.data_as(_lib._up)))
         conv = conv.astype(bool)
+        self._finalize_callbacks()
         return bool(conv[0]) if self.problem.B == 1 else conv
 
     def solveFetch(self, init_xs, init_us, maxiter=100, isFeasible=False, regInit=1e-9):
@@ -281,7 +304,13 @@ class SolverDDP(object):
             self._install_callbacks(maxiter)
         check(lib().cgx_solver_solve_fetch(self._h, dptr(xs), dptr(us), int(maxiter), int(bool(isFeasible)), reg,
                                            conv.ctypes.data_as(_lib._up), dptr(xs_out), dptr(us_out)))
+        self._finalize_callbacks()
         return conv.astype(bool), xs_out, us_out
+
+    def _finalize_callbacks(self):
+        for cb_ in self._callbacks:
+            if hasattr(cb_, "finalize"):
+                cb_.finalize(self)
 
     def setCandidate(self, xs_warm=None, us_warm=None, isFeasible=False):
         xs, us = self._traj(xs_warm, us_warm)

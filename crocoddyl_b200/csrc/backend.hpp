@@ -104,6 +104,8 @@ struct Backend {
   virtual void export_status(int which /*0 backward, 1 forward*/, int* d_out) = 0;
   virtual void set_reg(double xreg, double ureg, bool set_x, bool set_u) = 0;
   virtual void export_trace(int b, double* d_out /*[cap][NTRACE]*/) = 0;
+  // records [0, nrec) of every problem in one go: d_out = [B][nrec][NTRACE] (nrec <= trace_cap)
+  virtual void export_trace_all(int nrec, double* d_out) = 0;
   // problem-level API (ShootingProblem::calc / calcDiff / rollout / quasiStatic)
   virtual void problem_calc(const double* d_xs, const double* d_us, int diff, double* d_costs) = 0;
   virtual void problem_rollout(const double* d_us, double* d_xs) = 0;

@@ -1,5 +1,6 @@
 // crocoddyl_b200 — extern "C" layer (include/crocoddyl_b200.h) over the CUDA backends.
 // No CPU fallback: every compute entry point needs a CUDA device and fails with CGX_ERR_CUDA otherwise.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -54,6 +55,7 @@ struct cgx_solver_s {
   bool has_xs = false, has_us = false;
   double* d_scal = nullptr;  // [B][17]
   PinnedDoubles h_scal;
+  PinnedDoubles h_trace;  // [B][nrec][NTRACE] for the callback replay
   int* d_status = nullptr;
   double* d_field = nullptr;  // scratch for accessors
   size_t field_cap = 0;
@@ -644,34 +646,39 @@ int cgx_solver_solve_fetch(cgx_solver_t s, const double* init_xs, const double* 
   if (s->cb) {
     CGX_TRY
     if (!s->be->trace_on) throw InvalidArg("callbacks need cgx_solver_enable_trace");
-    const int B = s->p->d.B, cap = s->be->trace_cap;
-    std::vector<double> rec((size_t)cap * NTRACE);
-    double* d = scratch(s, rec.size());
-    for (int b = 0; b < B; ++b) {
-      int n = (int)s->h_scal[(size_t)b * 17 + 12];
-      if (n > cap) n = cap;
-      if (n == 0) continue;
-      s->be->export_trace(b, d);
-      CGX_CUDA(cudaMemcpyAsync(rec.data(), d, rec.size() * sizeof(double), cudaMemcpyDeviceToHost, s->be->stream));
+    // the whole trace block comes back with one kernel and one copy into page-locked memory, then is replayed here
+    const int B = s->p->d.B;
+    int nrec = 0;
+    for (int b = 0; b < B; ++b) nrec = std::max(nrec, (int)s->h_scal[(size_t)b * 17 + 12]);
+    nrec = std::min(nrec, s->be->trace_cap);
+    if (nrec > 0) {
+      const size_t cnt = (size_t)B * nrec * NTRACE;
+      double* d = scratch(s, cnt);
+      s->h_trace.resize(cnt);
+      s->be->export_trace_all(nrec, d);
+      CGX_CUDA(cudaMemcpyAsync(s->h_trace.data(), d, cnt * sizeof(double), cudaMemcpyDeviceToHost, s->be->stream));
       CGX_CUDA(cudaStreamSynchronize(s->be->stream));
-      for (int i = 0; i < n; ++i) {
-        const double* r = rec.data() + (size_t)i * NTRACE;
-        cgx_iter_record ir;
-        ir.problem = b;
-        ir.iter = (int)r[0];
-        ir.cost = r[1];
-        ir.stop = r[2];
-        ir.d0 = r[3];
-        ir.d1 = r[4];
-        ir.xreg = r[5];
-        ir.ureg = r[6];
-        ir.steplength = r[7];
-        ir.is_feasible = (int)r[8];
-        ir.dV = r[9];
-        ir.dVexp = r[10];
-        ir.alpha_index = (int)r[11];
-        ir.retries = (int)r[12];
-        s->cb(s->cb_user, &ir);
+      for (int b = 0; b < B; ++b) {
+        const int n = std::min((int)s->h_scal[(size_t)b * 17 + 12], nrec);
+        for (int i = 0; i < n; ++i) {
+          const double* r = s->h_trace.data() + ((size_t)b * nrec + i) * NTRACE;
+          cgx_iter_record ir;
+          ir.problem = b;
+          ir.iter = (int)r[0];
+          ir.cost = r[1];
+          ir.stop = r[2];
+          ir.d0 = r[3];
+          ir.d1 = r[4];
+          ir.xreg = r[5];
+          ir.ureg = r[6];
+          ir.steplength = r[7];
+          ir.is_feasible = (int)r[8];
+          ir.dV = r[9];
+          ir.dVexp = r[10];
+          ir.alpha_index = (int)r[11];
+          ir.retries = (int)r[12];
+          s->cb(s->cb_user, &ir);
+        }
       }
     }
     CGX_CATCH

@@ -2,6 +2,8 @@
 // instantiated in one translation unit per model (cta_backend.cu: LQR and the factory; cta_arm{2,4,7}.cu: the
 // revolute-chain arm) so that the models compile in parallel.
 #pragma once
+#include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include "backend.hpp"
@@ -225,15 +227,23 @@ struct CtaBackend : Backend {
     }
     cta_phase_init_kernel<<<sblocks(), 128, 0, stream>>>(c, maxiter, is_feasible, reginit);
     ++last_launches;
-    // upper bound of rounds: every round an unfinished problem either runs a backward pass or a trial
-    const long max_rounds = (long)maxiter * (c.o.nalphas + 64) + RING;
+    // upper bound of rounds: every round an unfinished problem either runs a backward pass (at most one per step of
+    // the regularisation from regmin to regmax, ddp.cpp:312-318) or a trial of the line search
+    const double span = std::log(std::max(c.o.regmax, 1e-300) / std::max(c.o.regmin, 1e-300)) / std::log(c.o.regfactor);
+    const long max_retries = (long)std::ceil(std::max(span, 0.)) + 2;
+    const long max_rounds = (long)maxiter * (c.o.nalphas + max_retries) + RING;
     long unfinished = c.B;  // last count that came back (never smaller than the truth)
+    long last_round = -1;
+    bool finished = false;
     for (long r = 0; r < max_rounds; ++r) {
       const int slot = (int)(r % RING);
       if (r >= RING - 1) {  // result of round r - (RING - 1)
         const int old = (int)((r - (RING - 1)) % RING);
         CGX_CUDA(cudaEventSynchronize(ring_ev[old]));
-        if (h_active[old] == 0) break;
+        if (h_active[old] == 0) {
+          finished = true;
+          break;
+        }
         unfinished = h_active[old];
       }
       // concurrent line search while all trials of the unfinished problems fit the GPU in one wave (cta.cuh)
@@ -256,6 +266,13 @@ struct CtaBackend : Backend {
       last_launches += 2;
       CGX_CUDA(cudaMemcpyAsync(h_active + slot, d_active + slot, sizeof(int), cudaMemcpyDeviceToHost, stream));
       CGX_CUDA(cudaEventRecord(ring_ev[slot], stream));
+      last_round = r;
+    }
+    if (!finished) {  // the round bound was hit: make sure that every problem has returned (backstop)
+      CGX_CUDA(cudaStreamSynchronize(stream));
+      if (last_round >= 0 && h_active[last_round % RING] != 0)
+        throw CudaError("phase-split solve: " + std::to_string(h_active[last_round % RING]) +
+                        " problems had not returned when the round bound was reached");
     }
   }
   void compute_direction(int recalc) override {
@@ -340,6 +357,13 @@ struct CtaBackend : Backend {
     if (!c.trace) throw InvalidArg("trace recording is not enabled (cgx_solver_enable_trace)");
     CGX_CUDA(cudaMemcpyAsync(d_out, c.trace + (size_t)b * c.trace_cap * NTRACE, (size_t)c.trace_cap * NTRACE * sizeof(double),
                              cudaMemcpyDeviceToDevice, stream));
+  }
+
+  void export_trace_all(int nrec, double* d_out) override {
+    if (!c.trace) throw InvalidArg("trace recording is not enabled (cgx_solver_enable_trace)");
+    if (nrec <= 0) return;
+    CGX_CUDA(cudaMemcpy2DAsync(d_out, (size_t)nrec * NTRACE * sizeof(double), c.trace, (size_t)c.trace_cap * NTRACE * sizeof(double),
+                               (size_t)nrec * NTRACE * sizeof(double), c.B, cudaMemcpyDeviceToDevice, stream));
   }
 
   // ---- problem-level API ----

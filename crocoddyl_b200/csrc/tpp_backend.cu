@@ -375,6 +375,7 @@ struct TppBackend : Backend {
   }
   void set_reg(double xreg, double ureg, bool set_x, bool set_u) override;
   void export_trace(int b, double* d_out) override;
+  void export_trace_all(int nrec, double* d_out) override;
 
   // ---- problem-level API ----
   void problem_calc(const double* d_xs, const double* d_us, int diff, double* d_costs) override;
@@ -466,6 +467,21 @@ template <class M>
 void TppBackend<M>::export_trace(int b, double* d_out) {
   if (!c.trace) throw InvalidArg("trace recording is not enabled (cgx_solver_enable_trace)");
   tpp_trace_kernel<<<(c.trace_cap * NTRACE + 63) / 64, 64, 0, stream>>>(c, b, d_out);
+}
+// trace [cap][NTRACE][Bp] -> [B][nrec][NTRACE]
+__global__ void tpp_trace_all_kernel(TppCtx c, int nrec, double* out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r = blockIdx.y;
+  if (b >= c.B) return;
+  for (int j = 0; j < NTRACE; ++j)
+    out[((size_t)b * nrec + r) * NTRACE + j] = c.trace[((size_t)r * NTRACE + j) * c.Bp + b];
+}
+template <class M>
+void TppBackend<M>::export_trace_all(int nrec, double* d_out) {
+  if (!c.trace) throw InvalidArg("trace recording is not enabled (cgx_solver_enable_trace)");
+  if (nrec <= 0) return;
+  tpp_trace_all_kernel<<<dim3(nblocks(), nrec), 64, 0, stream>>>(c, nrec, d_out);
+  ++last_launches;
 }
 template <class M>
 void TppBackend<M>::problem_calc(const double* d_xs, const double* d_us, int diff, double* d_costs) {

@@ -175,19 +175,39 @@ def test_problem_calc_calcdiff_rollout():
 
 
 def test_callbacks_replay_iterations():
+    """CallbackLogger carries the reference's attributes (bindings/python/crocoddyl/__init__.py:356-381), one entry per
+    iteration, replayed from the device trace (one copy for the whole batch)."""
     B, T = 8, 20
     x0, problem, solver, ob = _pair("fddp", B, T, 21)
-    log = cb.CallbackLogger()
-    solver.setCallbacks([log])
+    logs = [cb.CallbackLogger(b) for b in range(B)]
+    seen = []
+    solver.setCallbacks(logs + [lambda rec: seen.append(rec["problem"])])
     xs = np.repeat(x0[:, None, :], T + 1, 1)
     solver.solve(xs, np.zeros((B, T, 2)), 100, False, 1e-9)
     ob.solve(xs, np.zeros((B, T, 2)), 100, False, 1e-9)
     n = solver.scalars()["n_records"]
-    assert len(log.records) == int(n.sum())
-    r0 = [r for r in log.records if r["problem"] == 0]
-    to = ob.trace(0)
-    assert [r["iter"] for r in r0] == list(to[:, 0].astype(int))
-    np.testing.assert_allclose([r["cost"] for r in r0], to[:, 1], rtol=1e-9)
+    assert len(seen) == int(n.sum())
+    for b, log in enumerate(logs):
+        to = ob.trace(b)
+        assert log.iters == list(to[:, 0].astype(int))
+        np.testing.assert_allclose(log.costs, to[:, 1], rtol=1e-9)
+        np.testing.assert_allclose(log.stops, to[:, 2], rtol=1e-6, atol=1e-12)
+        np.testing.assert_allclose(log.grads, -to[:, 4], rtol=1e-6, atol=1e-9)
+        assert log.x_regs == list(to[:, 5]) and log.u_regs == list(to[:, 6]) and log.steps == list(to[:, 7])
+        np.testing.assert_allclose(np.array(log.xs), ob.get_all("xs", b), rtol=1e-9, atol=1e-9)
+        np.testing.assert_allclose(np.array(log.us), ob.get_all("us", b), rtol=1e-9, atol=1e-9)
+        assert len(log.fs) == 1 and np.array(log.fs[0]).shape == (T + 1, 3)
+    # the arm backend (trace stored [B][cap][.]) goes through the same replay
+    nv = 4
+    arm = cb.ArmActionModel(cb.synthetic_arm(nv), 1e-3)
+    xa = np.concatenate([np.random.default_rng(1).uniform(-1, 1, (3, nv)), np.zeros((3, nv))], 1)
+    pa = cb.ShootingProblem(xa, [arm] * 6, arm.terminal_model)
+    sa = cb.SolverFDDP(pa)
+    la = cb.CallbackLogger(2)
+    sa.setCallbacks([la])
+    sa.solve(np.repeat(xa[:, None, :], 7, 1), np.repeat(pa.quasiStatic(xa)[:, None, :], 6, 1), 10, False, 0.1)
+    assert len(la.costs) == int(sa.scalars()["n_records"][2]) and len(la.costs) > 0
+    np.testing.assert_allclose(la.costs[-1], sa.scalars()["cost"][2], rtol=1e-12)
 
 
 @pytest.mark.parametrize("kind", ["ddp", "fddp"])

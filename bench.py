@@ -43,9 +43,10 @@ class Unicycle(object):
     default_batch, cpu_sample = 65536, 8192
     kernel = "tpp_solve_kernel<UnicycleModel>"
     oracle_kind = "unicycle"
-    # algorithmic HBM bytes per node of the lean storage policy: useful doubles only
-    bytes_bwd = 8 * (3 + 2 + 3 + 2 * 3 + 2 + 3 + 3 + 6)  # read xs,us ; write fs,K,k,w,Vx,tril(Vxx)
-    bytes_fwd = 8 * (3 + 2 + 2 * 3 + 2 + 3 + 3 + 3 + 2)  # read xs,us,K,k,fs,w ; write xs_try,us_try
+    # algorithmic HBM bytes per node, SURVEY 8(d): B_fused = 8(n+m) read + 8(mn+3m+3n) written (K,k,Qu,Quuk,Vx,w,fs);
+    # B_roll = 8(3n+3m+mn) per trial (read xs,us,K,k,fs ; write xs_try,us_try); first calc reads xs,us
+    bytes_bwd = 8 * (3 + 2) + 8 * (2 * 3 + 3 * 2 + 3 * 3)  # 208
+    bytes_fwd = 8 * (3 * 3 + 3 * 2 + 2 * 3)                # 168
     bytes_calc = 8 * (3 + 2)
 
     def describe(self, B):
@@ -190,7 +191,7 @@ def host_threads():
         return max(1, os.cpu_count() or 1)
 
 
-def cpu_oracle_rate(wl, nsample, nthreads=0, reps=1):
+def cpu_oracle_rate(wl, nsample, nthreads=0, reps=1, want_scalars=False):
     """Reference algorithm on the host cores: oracle, -O3 build, OpenMP over problems."""
     import oracle_lib as ol
 
@@ -203,18 +204,29 @@ def cpu_oracle_rate(wl, nsample, nthreads=0, reps=1):
         ob.solve(xs, us, 100, False, wl.reginit, nthreads=nthreads)
         best = ob.seconds if best is None else min(best, ob.seconds)
     cores = ob.lib.orc_max_threads() if nthreads <= 0 else nthreads
+    if want_scalars:
+        return nsample / best, cores, best, ob.scalars()
     return nsample / best, cores, best
 
 
+def build_oracle_only():
+    """The CPU legs need the oracle alone: make -C oracle (the product library is neither built nor loaded here)."""
+    out = subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+    if out.returncode != 0:
+        sys.stderr.write(out.stdout.decode())
+        raise RuntimeError("oracle build failed")
+
+
 def run_reference(args, wl, rank, world):
+    """--impl reference: the reference algorithm's CPU implementation (oracle port, -O3, OpenMP over problems, all host
+    threads) on the SAME workload as the GPU arm at N = 1: every step solves all default_batch problems of config C2
+    (65,536; about 4 s per step on 16 threads). Rank 0 only; never touches the product library."""
     if rank != 0:
         return
-    import __graft_entry__ as ge
-
-    ge.build(quiet=True)
+    build_oracle_only()
     import oracle_lib as ol
 
-    nsample = wl.cpu_sample
+    nsample = args.batch or wl.default_batch
     params, x0, xs, us = oracle_inputs(wl, nsample)
     ob = ol.OracleBatch(wl.oracle_kind, "fddp", T, wl.nx, wl.nu, params, x0, fast=True)
     cores = host_threads()
@@ -225,18 +237,170 @@ def run_reference(args, wl, rank, world):
             times.append(ob.seconds)
     tot = sum(times)
     value = nsample * len(times) / tot
-    sample = "first %d problems of the workload per step (same seeds), OpenMP over problems, %d threads" % (nsample, cores)
+    sample = "all %d problems of the workload per step (same seeds as the GPU arm), OpenMP over problems, %d threads" % (nsample, cores)
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": wl.describe(nsample), "problems_per_step": nsample,
-                   "note": "CPU port of the reference algorithm (oracle/, -O3, OpenMP over problems); the reference itself "
-                           "needs Eigen+Boost(+Pinocchio), which this image lacks"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "config": {"workload": wl.describe(nsample), "problems_per_gpu": nsample, "problems_total": nsample,
+                   "note": "CPU port of the reference algorithm (oracle/, -O3, OpenMP over problems, pinned to the reference "
+                           "by tests/golden/ref_golden.npz); the reference itself needs Eigen+Boost(+Pinocchio), which this "
+                           "image lacks. One host: the rate does not grow with --gpus."},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "sample_frac": 1.0},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+class Runner(object):
+    """One workload on this rank's GPU: resident (`value`) and end-to-end timing of `steps` solves, max over ranks."""
+
+    def __init__(self, wl, rank, local_rank, world, dist, batch=0, batch_total=0):
+        import torch
+        import crocoddyl_b200 as cb
+        from crocoddyl_b200 import sharding
+
+        self.wl, self.rank, self.world, self.dist = wl, rank, world, dist
+        self.torch, self.cb, self.sharding = torch, cb, sharding
+        if batch_total:  # strong scaling: one global batch, contiguous shards (SURVEY 8e, config C5)
+            self.total, self.scaling = batch_total, "strong"
+            lo, hi = sharding.shard_range(batch_total, rank, world)
+            x0, xs_np, us_np = wl.inputs(lo, hi, batch_total, 0)
+        else:  # weak scaling: the same per-GPU batch on every rank, different seeds
+            B0 = batch or wl.default_batch
+            self.total, self.scaling = B0 * world, "weak"
+            x0, xs_np, us_np = wl.inputs(0, B0, B0, 1000 * rank)
+        self.B = B = x0.shape[0]
+        model = wl.model()
+        self.problem = cb.ShootingProblem(x0, [model] * T, wl.terminal(model))
+        if us_np is None:
+            us_np = np.repeat(self.problem.quasiStatic(x0)[:, None, :], T, 1)
+        # pinned host buffers (what a caller hands to the reference-facing API)
+        self.xs_h = torch.from_numpy(np.ascontiguousarray(xs_np)).pin_memory()
+        self.us_h = torch.from_numpy(np.ascontiguousarray(us_np)).pin_memory()
+        self.xs_out = torch.empty_like(self.xs_h).pin_memory()
+        self.us_out = torch.empty_like(self.us_h).pin_memory()
+        self.solver = cb.SolverFDDP(self.problem)
+        self.solver.setStorage(False)  # lean: keeps xs, us, K, k, Vx, Vxx, fs (the accessors north_star names)
+        self.conv = np.zeros(B, dtype=np.uint8)
+        self.scal = np.zeros((B, 17))
+        self.dev = torch.device("cuda", local_rank)
+
+    def dp(self, t):
+        import ctypes as C
+        return C.cast(t.data_ptr(), C.POINTER(C.c_double))
+
+    def gather_results(self):
+        # the one collective of the path: per-problem {cost, iter, stop, converged} to every rank
+        return self.sharding.gather_records(self.sharding.records_from_scalars(self.scal), self.total, self.dist, self.dev)
+
+    def step_resident(self):
+        import ctypes as C
+        cb, L, h = self.cb, self.cb.lib(), self.solver._h
+        cb.check(L.cgx_solver_solve_resident(h, 100, 0, self.wl.reginit))
+        cb.check(L.cgx_solver_download(h, self.conv.ctypes.data_as(C.POINTER(C.c_ubyte))))
+        cb.check(L.cgx_solver_get_scalars(h, cb.dptr(self.scal)))
+        self.gather_results()
+        return self.solver.timing()
+
+    def step_e2e(self):
+        # solve() + the xs/us getters as one reference-facing call (cgx_solver_solve_fetch): pinned host -> device ->
+        # solve -> pinned host; the unicycle backend slices the batch so that the copies overlap the solve
+        import ctypes as C
+        cb, L, h = self.cb, self.cb.lib(), self.solver._h
+        cb.check(L.cgx_solver_solve_fetch(h, self.dp(self.xs_h), self.dp(self.us_h), 100, 0, self.wl.reginit,
+                                          self.conv.ctypes.data_as(C.POINTER(C.c_ubyte)), self.dp(self.xs_out),
+                                          self.dp(self.us_out)))
+        cb.check(L.cgx_solver_get_scalars(h, cb.dptr(self.scal)))
+        self.gather_results()
+
+    def sync(self):
+        self.torch.cuda.synchronize()
+        if self.dist is not None:
+            self.dist.barrier()
+            self.torch.cuda.synchronize()
+
+    def run(self, steps, warmup, sampler=None):
+        torch, cb, wl, dist = self.torch, self.cb, self.wl, self.dist
+        L, h = cb.lib(), self.solver._h
+        cb.check(L.cgx_solver_upload(h, self.dp(self.xs_h), self.dp(self.us_h)))
+        for _ in range(warmup):
+            self.step_resident()
+        if sampler is not None:
+            sampler.start()
+        self.sync()
+        call_ms, kern_ms, launches = [], [], 0
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            tm = self.step_resident()
+            call_ms.append(tm["call_ms"])
+            kern_ms.append(tm["kernel_ms"])
+            launches += tm["launches"] + 1  # + the scalar export kernel
+        self.sync()
+        wall_ms = 1e3 * (time.perf_counter() - t0)
+        clocks = sampler.stop() if sampler is not None else None
+        dev_ms = float(np.sum(call_ms))
+        sg = self.solver.scalars()
+        nb, nf = sg["n_backward"], sg["n_forward"]
+        alg_bytes = float(T * (nb * wl.bytes_bwd + (nf - 1) * wl.bytes_fwd + wl.bytes_calc).sum())
+        records = self.gather_results()
+        for _ in range(max(2, min(warmup, 3))):
+            self.step_e2e()
+        self.sync()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            self.step_e2e()
+        self.sync()
+        e2e_ms = 1e3 * (time.perf_counter() - t0)
+        # the fused call must have delivered exactly what the accessors hold (outside the timed region)
+        chk = torch.empty_like(self.xs_out)
+        cb.check(L.cgx_solver_get_all(h, b"xs", self.dp(chk)))
+        if not torch.equal(chk, self.xs_out):
+            raise RuntimeError("cgx_solver_solve_fetch: xs_out differs from cgx_solver_get_all(xs)")
+        if dist is not None:
+            v = torch.tensor([dev_ms, e2e_ms, wall_ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(v, op=dist.ReduceOp.MAX)
+            dev_ms, e2e_ms, wall_ms = [float(a) for a in v.cpu()]
+        solved = self.total * steps
+        kms = float(np.mean(kern_ms))
+        h2d = int(self.xs_h.numel() * 8 + self.us_h.numel() * 8)
+        d2h = int(self.xs_out.numel() * 8 + self.us_out.numel() * 8 + self.scal.size * 8 * 2 + self.B)
+        res = {
+            "value": solved / (dev_ms * 1e-3), "ms_per_step": dev_ms / steps, "scaling": self.scaling,
+            "problems_per_gpu": self.B, "problems_total": self.total,
+            "e2e": {"value": solved / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_ms / steps,
+                    "host_copy_gbs_per_rank": (h2d + d2h) / (e2e_ms / steps * 1e-3) / 1e9},
+            "gpu_launches": int(launches), "clocks": clocks, "wall_ms_per_step": wall_ms / steps,
+            "solve_stats": {"iterations_mean": float(records[:, 1].mean()), "converged_frac": float(records[:, 3].mean()),
+                            "backward_sweeps_mean": float(nb.mean()), "forward_sweeps_mean": float(nf.mean())},
+            "kernel_ms": kms, "algorithmic_bytes_per_launch": alg_bytes, "scalars": sg,
+        }
+        return res
+
+
+def fp64_view(wl, res, fp64_peak):
+    sg = res["scalars"]
+    nb, nf, nrec = sg["n_backward"], sg["n_forward"], sg["n_records"]
+    flops = float((T * nb * wl.flops_ric + (T + 1) * ((nrec + 1) * wl.flops_calcdiff + (nf + 1) * wl.flops_calc)).sum())
+    tf = flops / (res["kernel_ms"] * 1e-3) / 1e12
+    return {"achieved": tf, "peak": fp64_peak, "unit": "TFLOP/s", "frac": tf / fp64_peak,
+            "peak_source": "measured on this GPU (cgx_probe_fp64_tflops, register-resident DFMA loop)",
+            "algorithmic_flops_per_step": flops,
+            "note": "this rank's problems; upper bound of calcDiff evaluations: one per accepted iteration + the first"}
+
+
+def traffic_record(kernel_key):
+    """DRAM bytes per launch of the dominant kernel from the ncu --set full capture of the CURRENT kernels, if committed."""
+    prof = os.path.join(ROOT, "profiles", "r02_traffic.json")
+    if os.path.exists(prof):
+        try:
+            d = json.load(open(prof))
+            if kernel_key in d:
+                return d[kernel_key].get("dram_bytes_per_launch"), d[kernel_key].get("source")
+        except Exception:
+            pass
+    return None, None
 
 
 def main():
@@ -249,6 +413,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="problems per GPU (weak scaling)")
     ap.add_argument("--batch-total", type=int, default=0, help="total problems split over the ranks (strong scaling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="only the headline workload (no C1 / C3 / C4 / C5 blocks)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -257,8 +422,6 @@ def main():
     if args.impl == "reference":
         run_reference(args, wl, rank, world)
         return
-
-    import ctypes as C
 
     import torch
     import __graft_entry__ as ge
@@ -273,118 +436,23 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         dist.barrier()
     import crocoddyl_b200 as cb
-    from crocoddyl_b200 import sharding
 
     cb.set_device(local_rank)
     torch.cuda.set_device(local_rank)
-    if args.batch_total:  # strong scaling: one global batch, contiguous shards
-        total, scaling = args.batch_total, "strong"
-        lo, hi = sharding.shard_range(total, rank, world)
-        x0, xs_np, us_np = wl.inputs(lo, hi, total, 0)
-    else:  # weak scaling: the same per-GPU batch on every rank, different seeds
-        B0 = args.batch or wl.default_batch
-        total, scaling = B0 * world, "weak"
-        lo, hi = rank * B0, (rank + 1) * B0
-        x0, xs_np, us_np = wl.inputs(0, B0, B0, 1000 * rank)
-    B = hi - lo
-    model = wl.model()
-    problem = cb.ShootingProblem(x0, [model] * T, wl.terminal(model))
-    if us_np is None:
-        us_np = np.repeat(problem.quasiStatic(x0)[:, None, :], T, 1)
-    # pinned host buffers (what a caller hands to the reference-facing API)
-    xs_h = torch.from_numpy(np.ascontiguousarray(xs_np)).pin_memory()
-    us_h = torch.from_numpy(np.ascontiguousarray(us_np)).pin_memory()
-    xs_out = torch.empty_like(xs_h).pin_memory()
-    us_out = torch.empty_like(us_h).pin_memory()
-    solver = cb.SolverFDDP(problem)
-    solver.setStorage(False)  # lean: keeps xs, us, K, k, Vx, Vxx, fs (the accessors north_star names)
-    L = cb.lib()
-    h = solver._h
-    conv = np.zeros(B, dtype=np.uint8)
-    scal = np.zeros((B, 17))
-    dev = torch.device("cuda", local_rank)
-
-    def dp(t):
-        return C.cast(t.data_ptr(), C.POINTER(C.c_double))
-
-    def gather_results():
-        # the one collective of the path: per-problem {cost, iter, stop, converged} to every rank
-        return sharding.gather_records(sharding.records_from_scalars(scal), total, dist, dev)
-
-    def step_resident():
-        cb.check(L.cgx_solver_solve_resident(h, 100, 0, wl.reginit))
-        cb.check(L.cgx_solver_download(h, conv.ctypes.data_as(C.POINTER(C.c_ubyte))))
-        cb.check(L.cgx_solver_get_scalars(h, cb.dptr(scal)))
-        gather_results()
-        return solver.timing()
-
-    def step_e2e():
-        # solve() + the xs/us getters as one reference-facing call (cgx_solver_solve_fetch): pinned host -> device ->
-        # solve -> pinned host; the unicycle backend slices the batch so that the copies overlap the solve
-        cb.check(L.cgx_solver_solve_fetch(h, dp(xs_h), dp(us_h), 100, 0, wl.reginit,
-                                          conv.ctypes.data_as(C.POINTER(C.c_ubyte)), dp(xs_out), dp(us_out)))
-        cb.check(L.cgx_solver_get_scalars(h, cb.dptr(scal)))
-        gather_results()
-
-    def sync():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    # ---- resident (value) -------------------------------------------------------------------
-    cb.check(L.cgx_solver_upload(h, dp(xs_h), dp(us_h)))
-    for _ in range(args.warmup):
-        step_resident()
-    sampler = ClockSampler(local_rank)
+    # ---- headline: BASELINE config C2 (or --workload arm) ---------------------------------------------------------
+    runner = Runner(wl, rank, local_rank, world, dist, args.batch, args.batch_total)
+    B, total = runner.B, runner.total
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    res = runner.run(args.steps, args.warmup, sampler)
+    line = None
     if rank == 0:
-        sampler.start()
-    sync()
-    call_ms, kern_ms, launches = [], [], 0
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        tm = step_resident()
-        call_ms.append(tm["call_ms"])
-        kern_ms.append(tm["kernel_ms"])
-        launches += tm["launches"] + 1  # + the scalar export kernel
-    sync()
-    wall_ms = 1e3 * (time.perf_counter() - t0)
-    clocks = sampler.stop() if rank == 0 else None
-    dev_ms = float(np.sum(call_ms))
-    sg = solver.scalars()
-    nb, nf = sg["n_backward"], sg["n_forward"]
-    alg_bytes = float(T * (nb * wl.bytes_bwd + (nf - 1) * wl.bytes_fwd + wl.bytes_calc).sum())
-    records = gather_results()
-    # ---- e2e ---------------------------------------------------------------------------------
-    for _ in range(2):
-        step_e2e()
-    sync()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step_e2e()
-    sync()
-    e2e_ms = 1e3 * (time.perf_counter() - t0)
-    # the fused call must have delivered exactly what the accessors hold (outside the timed region)
-    chk = torch.empty_like(xs_out)
-    cb.check(L.cgx_solver_get_all(h, b"xs", dp(chk)))
-    if not torch.equal(chk, xs_out):
-        raise RuntimeError("cgx_solver_solve_fetch: xs_out differs from cgx_solver_get_all(xs)")
-    if dist is not None:
-        v = torch.tensor([dev_ms, e2e_ms, wall_ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(v, op=dist.ReduceOp.MAX)
-        dev_ms, e2e_ms, wall_ms = [float(a) for a in v.cpu()]
-    if rank == 0:
-        solved = total * args.steps
-        value = solved / (dev_ms * 1e-3)
         peak, peak_src = hbm_peak()
-        kms = float(np.mean(kern_ms))
-        achieved = alg_bytes / (kms * 1e-3) / 1e9
-        h2d = int(xs_h.numel() * 8 + us_h.numel() * 8)
-        d2h = int(xs_out.numel() * 8 + us_out.numel() * 8 + scal.size * 8 * 2 + B)
-        ws_gb = (2 * xs_h.numel() + 2 * us_h.numel()) * 8 / 1e9
+        achieved = res["algorithmic_bytes_per_launch"] / (res["kernel_ms"] * 1e-3) / 1e9
+        ws_gb = (2 * runner.xs_h.numel() + 2 * runner.us_h.numel()) * 8 / 1e9
+        traffic, traffic_src = traffic_record(wl.name) if (B == wl.default_batch) else (None, None)
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": scaling,
+            "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": res["scaling"],
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": wl.describe(B), "problems_per_gpu": B, "problems_total": total,
                        "storage": "lean (xs,us,K,k,Vx,Vxx,fs kept)",
@@ -392,42 +460,81 @@ def main():
                              "solver state" % ws_gb,
                        "parallelism": "independent OCPs sharded over %d rank(s); NCCL all-gather of per-problem "
                        "{cost,iter,stop,converged}" % world},
-            "e2e": {"value": solved / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": e2e_ms / args.steps},
-            "gpu_launches": int(launches),
-            "clocks": clocks,
-            "wall_ms_per_step": wall_ms / args.steps,
-            "solve_stats": {"iterations_mean": float(records[:, 1].mean()), "converged_frac": float(records[:, 3].mean()),
-                            "backward_sweeps_mean": float(nb.mean()), "forward_sweeps_mean": float(nf.mean())},
+            "e2e": res["e2e"], "gpu_launches": res["gpu_launches"], "clocks": res["clocks"],
+            "wall_ms_per_step": res["wall_ms_per_step"], "solve_stats": res["solve_stats"],
             "roofline": {"kernel": wl.kernel, "bound": "hbm", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": kms},
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src, "algorithmic_bytes_per_launch": res["algorithmic_bytes_per_launch"],
+                         "bytes_per_node": {"backward": wl.bytes_bwd, "forward": wl.bytes_fwd, "first_calc": wl.bytes_calc,
+                                            "source": "SURVEY 8(d): B_fused / B_roll"},
+                         "kernel_ms": res["kernel_ms"]},
         }
-        if hasattr(wl, "flops_ric"):  # arm: the FP64 view of the same step (north_star: Riccati / ABA-derivative kernels)
-            nrec = sg["n_records"]
-            flops = float((T * nb * wl.flops_ric + (T + 1) * ((nrec + 1) * wl.flops_calcdiff + (nf + 1) * wl.flops_calc)).sum())
-            fp64_peak = cb.probe_fp64_tflops()
-            line["fp64"] = {"achieved": flops / (kms * 1e-3) / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
-                            "frac": flops / (kms * 1e-3) / 1e12 / fp64_peak,
-                            "peak_source": "measured on this GPU (cgx_probe_fp64_tflops, register-resident DFMA loop)",
-                            "algorithmic_flops_per_step": flops,
-                            "note": "upper bound of calcDiff evaluations: one per accepted iteration + the first"}
+        fp64_peak = cb.probe_fp64_tflops()
+        if hasattr(wl, "flops_ric"):
+            line["fp64"] = fp64_view(wl, res, fp64_peak)
         if not args.no_cpu_baseline:
-            nsample = wl.cpu_sample
-            rate, cores, sec = cpu_oracle_rate(wl, nsample)
+            nsample = min(wl.cpu_sample, B)
+            rate, cores, sec, so = cpu_oracle_rate(wl, nsample, want_scalars=True)
             line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": "first %d problems of the same workload, %.2f s, OpenMP over problems" %
-                                    (nsample, sec)}
-        prof = os.path.join(ROOT, "profiles", "traffic_r01.json")
-        if os.path.exists(prof) and wl.name == "unicycle" and B == 65536:
-            try:
-                line["roofline"]["traffic"] = json.load(open(prof)).get("tpp_solve_kernel_dram_bytes_per_launch")
-            except Exception:
-                pass
+                                    (nsample, sec), "sample_frac": nsample / float(B)}
+            if not args.batch_total:  # the sample is the head of rank 0's own problems: how often do the counts agree?
+                same = so["n_records"] == res["scalars"]["n_records"][:nsample]
+                line["solve_stats"]["iter_parity_frac"] = float(same.mean())
+                line["solve_stats"]["iter_parity_note"] = ("identical iteration count GPU vs CPU oracle on the cpu_baseline "
+                                                           "sample; floor set by libm rounding: profiles/r02_sincos_sensitivity.json")
+    # ---- the other BASELINE configs, same process, same JSON line -------------------------------------------------
+    if not args.no_extras and args.workload == "unicycle" and not args.batch and not args.batch_total:
+        del runner
+        extras = run_extras(args, rank, local_rank, world, dist, cb, line)
+        if rank == 0:
+            line.update(extras)
+    if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def run_extras(args, rank, local_rank, world, dist, cb, line):
+    """C1 (single LQR OCP, ms per call), C3 (Riccati us per problem-sweep, FP64 fraction), C4 (arm B = 1024) at N = 1;
+    C5 (arm, B = 8192 SPLIT over the ranks: strong scaling) at every N."""
+    out = {}
+    arm = Arm()
+    steps, warmup = min(args.steps, 3), 3
+    fp64_peak = cb.probe_fp64_tflops() if rank == 0 else None
+    if world == 1:
+        import bench_riccati
+
+        ric = bench_riccati.run(peak_tflops=fp64_peak)
+        out["riccati"] = [{"nx": r["nx"], "nu": r["nu"], "B": r["B"], "us_per_iter": r["us_per_problem_sweep"],
+                           "sweep_ms_batched": r["sweep_ms_batched"], "fp64_tflops": r["fp64_tflops"], "frac": r["frac"]}
+                          for r in ric]
+        out["riccati_note"] = ("C3: one SolverDDP::backwardPass per problem, LQR nx in {12,36,72}, nu = nx/3, T=100, B=4096; "
+                               "us_per_iter = batched sweep time / B; frac = F_ric flops / measured DFMA peak %.1f TFLOP/s" % fp64_peak)
+        c1 = bench_riccati.run_c1(trials=300, cpu_trials=100)
+        out["c1"] = {"ms_per_call": c1["gpu_call"]["mean_ms"], "ms_min": c1["gpu_call"]["min_ms"], "ms_max": c1["gpu_call"]["max_ms"],
+                     "kernel_ms": c1["gpu_kernel"]["mean_ms"], "cpu_port_1thread_ms": c1["cpu_oracle_1thread"]["mean_ms"],
+                     "config": c1["config"]}
+        r4 = Runner(arm, rank, local_rank, world, dist, batch=1024)
+        a4 = r4.run(steps, warmup)
+        out["arm_c4"] = {"solves_per_s": a4["value"], "ms_per_step": a4["ms_per_step"], "e2e": a4["e2e"],
+                         "fp64": fp64_view(arm, a4, fp64_peak), "solve_stats": a4["solve_stats"],
+                         "gpu_launches": a4["gpu_launches"], "config": arm.describe(1024)}
+        if not args.no_cpu_baseline:
+            rate, cores, sec, _ = cpu_oracle_rate(arm, arm.cpu_sample, want_scalars=True)
+            out["arm_c4"]["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+                                             "sample": "first %d problems, %.2f s" % (arm.cpu_sample, sec)}
+        del r4
+    r5 = Runner(arm, rank, local_rank, world, dist, batch_total=8192)
+    a5 = r5.run(steps, warmup)
+    if rank == 0:
+        out["arm_c5"] = {"solves_per_s": a5["value"], "ms_per_step": a5["ms_per_step"], "e2e": a5["e2e"], "scaling": "strong",
+                         "problems_total": 8192, "problems_per_gpu": a5["problems_per_gpu"], "n_gpus": world,
+                         "fp64": fp64_view(arm, a5, fp64_peak), "solve_stats": a5["solve_stats"],
+                         "strong_efficiency_inputs": "solves_per_s at n_gpus = N over N x solves_per_s at n_gpus = 1",
+                         "config": "C5: " + arm.describe(a5["problems_per_gpu"]) + "; 8192 problems split contiguously over the ranks"}
+    return out
 
 
 if __name__ == "__main__":

@@ -6,7 +6,8 @@
 // HBM layout ("lane-sector" records): every per-node quantity of problem b lives in a small record made of
 // whole 32-byte sectors, records of consecutive problems are adjacent:
 //     rec(t, b) = base + (t*Bp + b) * R        (R = record size in doubles, a multiple of 4)
-//   XU[2] : { x[N], u[U], fs[N] }      candidate / trial (double-buffered, picked by I_CUR)
+//   XU[2] : { x[N], u[U], aux | fs[N] } candidate / trial (double-buffered, picked by I_CUR); aux = what calc leaves
+//           for calcDiff (unicycle: sin/cos of the heading), fs in its own sector(s)
 //   KK    : { K[U*N] column-major, k[U] }
 //   V     : { w[N] = Vxx fs, Vx[N], lower triangle of Vxx (column-major) }
 //   Q     : { Qxx, Qxu, Quu, Qx, Qu }  only with full storage
@@ -58,7 +59,11 @@ template <class M>
 struct TppLayout {
   static constexpr int N = M::NX, U = M::NU;
   static constexpr int NL = N * (N + 1) / 2;
-  static constexpr int XU_X = 0, XU_U = N, XU_F = N + U, R_XU = rup4(2 * N + U);
+  // candidate / trial record: { x[N], u[U], aux[NA] | fs[N] } — the first group (whole sectors) is what a rollout
+  // writes and a backward pass reads; aux = per-node values calc leaves for calcDiff (unicycle: sin, cos of the heading,
+  // so that the backward pass needs no sincos of its own); the gaps have their own sector(s)
+  static constexpr int NA = M::NAUX;
+  static constexpr int XU_X = 0, XU_U = N, XU_A = N + U, XU_F = rup4(N + U + NA), R_XU = XU_F + rup4(N);
   static constexpr int KK_K = 0, KK_k = U * N, R_KK = rup4(U * N + U);
   static constexpr int V_W = 0, V_VX = N, V_VXX = 2 * N, R_V = rup4(2 * N + NL);
   static constexpr int Q_XX = 0, Q_XU = N * N, Q_UU = Q_XU + N * U, Q_X = Q_UU + U * U, Q_U = Q_X + N,
@@ -98,19 +103,23 @@ __device__ __forceinline__ void pf_rec(const double* p) {
 struct UnicycleModel {
   static constexpr int NX = 3;
   static constexpr int NU = 2;
+  static constexpr int NAUX = 2;  // sin, cos of x[2]: computed by calc, reused by calcDiff (unicycle.hxx:30-31,57-58)
+  // Structure of the derivatives (unicycle.hxx:45-73, data ctor unicycle.hpp:78-80): 0 = identically zero, 1 = one,
+  // 2 = general. The Riccati products skip the structural zeros (x + 0*y = x for finite y) and do not multiply by the
+  // ones, in the reference's summation order: same values, a third of the multiply-adds.
+  __host__ __device__ static constexpr int fx_kind(int i, int j) { return i == j ? 1 : ((j == 2 && i < 2) ? 2 : 0); }
+  __host__ __device__ static constexpr int fu_kind(int i, int j) { return ((j == 0 && i < 2) || (j == 1 && i == 2)) ? 2 : 0; }
+  __host__ __device__ static constexpr int lxx_kind(int i, int j) { return i == j ? 2 : 0; }
+  __host__ __device__ static constexpr int lxu_kind(int, int) { return 0; }
+  __host__ __device__ static constexpr int luu_kind(int i, int j) { return i == j ? 2 : 0; }
   double dt, w0, w1;
   __device__ void load(const double* p) {
     dt = p[0];
     w0 = p[1];
     w1 = p[2];
   }
-  // calc: xnext, cost (unicycle.hxx:22-42)
-  __device__ double calc(const double* x, const double* u, double* xnext) const {
-    double s, c;
-    sincos(x[2], &s, &c);
-    xnext[0] = x[0] + c * u[0] * dt;
-    xnext[1] = x[1] + s * u[0] * dt;
-    xnext[2] = x[2] + u[1] * dt;
+  // cost (unicycle.hxx:38-41)
+  __device__ double cost(const double* x, const double* u) const {
     double rr = 0.;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
@@ -124,25 +133,28 @@ struct UnicycleModel {
     }
     return 0.5 * rr;
   }
-  // calc + calcDiff in one go (one sincos). Matrices column-major. (unicycle.hxx:45-73)
-  __device__ double calcBoth(const double* x, const double* u, double* xnext, double* Fx, double* Fu, double* Lx,
-                             double* Lu, double* Lxx, double* Lxu, double* Luu) const {
+  // calc: xnext, cost (unicycle.hxx:22-42); aux = {sin, cos}
+  __device__ double calc(const double* x, const double* u, double* xnext, double* aux) const {
     double s, c;
     sincos(x[2], &s, &c);
+    aux[0] = s;
+    aux[1] = c;
     xnext[0] = x[0] + c * u[0] * dt;
     xnext[1] = x[1] + s * u[0] * dt;
     xnext[2] = x[2] + u[1] * dt;
-    double rr = 0.;
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      const double r = w0 * x[i];
-      rr += r * r;
-    }
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const double r = w1 * u[i];
-      rr += r * r;
-    }
+    return cost(x, u);
+  }
+  __device__ double calc(const double* x, const double* u, double* xnext) const {
+    double aux[2];
+    return calc(x, u, xnext, aux);
+  }
+  // calc + calcDiff in one go from the sin / cos calc left in aux. Matrices column-major. (unicycle.hxx:45-73)
+  __device__ double calcBothAux(const double* x, const double* u, const double* aux, double* xnext, double* Fx,
+                                double* Fu, double* Lx, double* Lu, double* Lxx, double* Lxu, double* Luu) const {
+    const double s = aux[0], c = aux[1];
+    xnext[0] = x[0] + c * u[0] * dt;
+    xnext[1] = x[1] + s * u[0] * dt;
+    xnext[2] = x[2] + u[1] * dt;
     const double wx = w0 * w0, wu = w1 * w1;
 #pragma unroll
     for (int i = 0; i < 9; ++i) {
@@ -172,7 +184,13 @@ struct UnicycleModel {
     Fu[0 + 3 * 0] = c * dt;
     Fu[1 + 3 * 0] = s * dt;
     Fu[2 + 3 * 1] = dt;
-    return 0.5 * rr;
+    return cost(x, u);
+  }
+  __device__ double calcBoth(const double* x, const double* u, double* xnext, double* Fx, double* Fu, double* Lx,
+                             double* Lu, double* Lxx, double* Lxu, double* Luu) const {
+    double aux[2];
+    sincos(x[2], &aux[0], &aux[1]);
+    return calcBothAux(x, u, aux, xnext, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);
   }
 };
 
@@ -188,28 +206,34 @@ struct UnicycleModel {
 #define TPP_REC(base, t, R) ((base) + ((size_t)(t) * (size_t)Bp + b) * (R))
 
 // ---------------------------------------------------------------------------------------------
-// problem_->calc(xs_, us_) in the reference's summation order (shooting.hxx:133-161): returns total cost.
+// problem_->calc(xs_, us_) in the reference's summation order (shooting.hxx:133-161): returns total cost and leaves
+// aux (what calcDiff reuses from calc) in every running node's record.
 template <class M>
-TPP_SWEEP_ATTR double tpp_calc_pass(const TppCtx& c, const M& m, int b, const double* __restrict__ xu) {
+TPP_SWEEP_ATTR double tpp_calc_pass(const TppCtx& c, const M& m, int b, double* __restrict__ xu) {
   typedef TppLayout<M> L;
-  constexpr int N = M::NX, U = M::NU, SXU = rup4(N + U) / 4;
+  constexpr int N = M::NX, U = M::NU, SXA = L::XU_F / 4, SA0 = L::XU_A / 4;
   const int Bp = c.Bp, T = c.T;
+  const size_t stride = (size_t)Bp * L::R_XU;
+  double* p = xu + (size_t)b * L::R_XU;
   double cost = 0.;
-  double rq[4 * SXU], r[4 * SXU], xn[N], u0[U];
-  ld_rec<0, SXU>(TPP_REC(xu, 0, L::R_XU), rq);
+  double rq[4 * SXA], r[4 * SXA], xn[N];
+  ld_rec<0, SXA>(p, rq);
   for (int t = 0; t < T; ++t) {
 #pragma unroll
-    for (int i = 0; i < 4 * SXU; ++i) r[i] = rq[i];
-    ld_rec<0, SXU>(TPP_REC(xu, t + 1, L::R_XU), rq);
-    if (t + TPP_PF_DIST <= T) pf_rec<0, SXU>(TPP_REC(xu, t + TPP_PF_DIST, L::R_XU));
-    cost += m.calc(r + L::XU_X, r + L::XU_U, xn);
+    for (int i = 0; i < 4 * SXA; ++i) r[i] = rq[i];
+    ld_rec<0, SXA>(p + stride, rq);
+    if (t + TPP_PF_DIST <= T) pf_rec<0, SXA>(p + TPP_PF_DIST * stride);
+    cost += m.calc(r + L::XU_X, r + L::XU_U, xn, r + L::XU_A);
+    st_rec<SA0, SXA>(p, r);
+    p += stride;
   }
-#pragma unroll
-  for (int i = 0; i < U; ++i) u0[i] = 0.;
   {
+    double u0[U];
+#pragma unroll
+    for (int i = 0; i < U; ++i) u0[i] = 0.;
     M mt;  // terminal model (loaded here: its parameters are live only for this node)
     mt.load(c.tparams);
-    cost += mt.calc(rq + L::XU_X, u0, xn);
+    cost += mt.cost(rq + L::XU_X, u0);
   }
   return cost;
 }
@@ -222,32 +246,67 @@ TPP_SWEEP_ATTR double tpp_calc_pass(const TppCtx& c, const M& m, int b, const do
 // because fs[t+1] = xnext(xs[t],us[t]) - xs[t+1] (ddp.cpp:160-171) needs node t's calc; the operations
 // and their order per node are unchanged. Vxx is exactly symmetric after ddp.cpp:235, so only its lower
 // triangle is carried and stored.
-template <class M, bool BOX = false>
-TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, bool recalc, bool is_feasible,
-                                bool was_feasible, double xreg, double ureg, double& dg_out, double& dq_out,
-                                double& stop_out) {
+// structured accumulation: s (+)= f * v where the factor f is structurally 0 (skip), 1 (add v) or general; `have`
+// says whether s already holds a term — both are compile-time constants once the loops are unrolled
+#define TPP_ACC(s, have, kind, f, v)             \
+  do {                                           \
+    if ((kind) == 1) {                           \
+      s = (have) ? s + (v) : (v);                \
+      have = true;                               \
+    } else if ((kind) == 2) {                    \
+      s = (have) ? s + (f) * (v) : (f) * (v);    \
+      have = true;                               \
+    }                                            \
+  } while (0)
+
+// fszero: bit i set = the gap sectors of candidate buffer i hold zeros (kept across the iterations of one solve so
+// that a feasible candidate zero-fills them once per buffer, ddp.cpp:172-176)
+// GAPS = !is_feasible: the feasible instantiation carries no gap / w arithmetic and no record of node t + 1 at all
+// (most sweeps of a solve run on a feasible candidate)
+template <class M, bool BOX, bool GAPS>
+TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, int b, int cur, bool recalc, double xreg, double ureg,
+                                     double& dg_out, double& dq_out, double& stop_out, int& fszero) {
+  constexpr bool is_feasible = !GAPS;
   typedef TppLayout<M> L;
   constexpr int N = M::NX, U = M::NU, NL = L::NL;
-  constexpr int SR = L::R_XU / 4, SF = L::XU_F / 4, SXU = rup4(N + U) / 4;
+  constexpr int SR = L::R_XU / 4, SXA = L::XU_F / 4;
   const int Bp = c.Bp, T = c.T;
   const bool fddp = c.fddp != 0;
   const bool full = c.full != 0;
-  double* xu = c.xu[cur];
+  const size_t sxu = (size_t)Bp * L::R_XU, skk = (size_t)Bp * L::R_KK, sv = (size_t)Bp * L::R_V;
+  double* pxu = c.xu[cur] + ((size_t)T * Bp + b) * L::R_XU;   // record of node t + 1 while node t is visited
+  double* pv = c.v + ((size_t)T * Bp + b) * L::R_V;
+  double* pkk = c.kk + ((size_t)(T - 1) * Bp + b) * L::R_KK;  // record of node t
   double dg = 0., dq = 0., stop = 0.;
   const bool has_xreg = !isnan(xreg), has_ureg = !isnan(ureg);  // ddp.cpp:185,216,226,237
+  // gaps: read back when they are not recomputed (only an infeasible candidate uses them)
+  const bool load_fs = GAPS && !recalc;
+  const bool zero_fs = !GAPS && recalc && !((fszero >> cur) & 1);
   double Vl[NL], Vx[N];
   double Fx[N * N], Fu[N * U], Lx[N], Lu[U], Lxx[N * N], Lxu[N * U], Luu[U * U], xn[N];
-  double rp[L::R_XU], r[L::R_XU], rq[L::R_XU];
+  // records in registers: rp = node t + 1 (x and the gaps: GAPS only), r = node t, rq = node t - 1 (prefetched)
+  constexpr int RW = GAPS ? L::R_XU : L::XU_F;  // the feasible instantiation never holds a gap sector
+  double rp[L::R_XU], r[RW], rq[RW];
+#pragma unroll
+  for (int i = 0; i < L::R_XU; ++i) rp[i] = 0.;
+#pragma unroll
+  for (int i = 0; i < RW; ++i) rq[i] = 0.;
   // terminal node (ddp.cpp:181-187): u = unone_ = 0 (action-base.hxx:27-37)
-  ld_rec<0, SR>(TPP_REC(xu, T, L::R_XU), rp);
-  ld_rec<0, SR>(TPP_REC(xu, T - 1, L::R_XU), rq);
+  ld_rec<0, SXA>(pxu, rp);
+  ld_rec<0, SXA>(pxu - sxu, rq);
+  if constexpr (GAPS) {
+    if (load_fs) {
+      ld_rec<SXA, SR>(pxu, rp);
+      ld_rec<SXA, SR>(pxu - sxu, rq);
+    }
+  }
   {
     double u0[U];
 #pragma unroll
     for (int i = 0; i < U; ++i) u0[i] = 0.;
     M mt;
     mt.load(c.tparams);
-    mt.calcBoth(rp + L::XU_X, u0, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);
+    mt.calcBothAux(rp + L::XU_X, u0, rp + L::XU_A, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);  // only Lx, Lxx are used
   }
 #pragma unroll
   for (int j = 0; j < N; ++j)
@@ -259,17 +318,22 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
   for (int t = T - 1; t >= -1; --t) {
     if (t >= 0) {
 #pragma unroll
-      for (int i = 0; i < L::R_XU; ++i) r[i] = rq[i];
+      for (int i = 0; i < RW; ++i) r[i] = rq[i];
       // software prefetch: node t-1's record is requested before node t's dependent Riccati chain starts,
       // node t-1-TPP_PF_DIST's record is pulled into L2
       if (t > 0) {
-        if (recalc)
-          ld_rec<0, SXU>(TPP_REC(xu, t - 1, L::R_XU), rq);
-        else
-          ld_rec<0, SR>(TPP_REC(xu, t - 1, L::R_XU), rq);
+        ld_rec<0, SXA>(pxu - 2 * sxu, rq);
+        if constexpr (GAPS) {
+          if (load_fs) ld_rec<SXA, SR>(pxu - 2 * sxu, rq);
+        }
       }
-      if (t > TPP_PF_DIST) pf_rec<0, SR>(TPP_REC(xu, t - 1 - TPP_PF_DIST, L::R_XU));
-      m.calcBoth(r + L::XU_X, r + L::XU_U, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);
+      if (t > TPP_PF_DIST) {
+        pf_rec<0, SXA>(pxu - (2 + TPP_PF_DIST) * sxu);
+        if constexpr (GAPS) {
+          if (load_fs) pf_rec<SXA, SR>(pxu - (2 + TPP_PF_DIST) * sxu);
+        }
+      }
+      m.calcBothAux(r + L::XU_X, r + L::XU_U, r + L::XU_A, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);
     } else {
       // gap of node 0: fs[0] = diff(xs[0], x0) = x0 - xs[0]   (ddp.cpp:162)
 #pragma unroll
@@ -279,13 +343,13 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
     double vrec[L::R_V];
 #pragma unroll
     for (int i = 0; i < L::R_V; ++i) vrec[i] = 0.;
-    if (!is_feasible) {
+    if constexpr (GAPS) {
       if (recalc) {
 #pragma unroll
         for (int i = 0; i < N; ++i) rp[L::XU_F + i] = xn[i] - rp[L::XU_X + i];
 #pragma unroll
         for (int i = L::XU_F + N; i < L::R_XU; ++i) rp[i] = 0.;
-        st_rec<SF, SR>(TPP_REC(xu, t + 1, L::R_XU), rp);
+        st_rec<SXA, SR>(pxu, rp);
       }
       const double* f = rp + L::XU_F;
 #pragma unroll
@@ -306,10 +370,10 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
         dg -= a;
         dq += q;
       }
-    } else if (recalc && !was_feasible) {
+    } else if (zero_fs) {
 #pragma unroll
       for (int i = L::XU_F; i < L::R_XU; ++i) rp[i] = 0.;  // ddp.cpp:172-176
-      st_rec<SF, SR>(TPP_REC(xu, t + 1, L::R_XU), rp);
+      st_rec<SXA, SR>(pxu, rp);
     }
     {
       double nrm = 0.;
@@ -321,7 +385,7 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
       }
 #pragma unroll
       for (int i = 0; i < NL; ++i) vrec[L::V_VXX + i] = Vl[i];
-      st_rec<0, L::R_V / 4>(TPP_REC(c.v, t + 1, L::R_V), vrec);
+      st_rec<0, L::R_V / 4>(pv, vrec);
       if (t + 1 < T && raise_if_nan(nrm)) return 1;  // ddp.cpp:246-248
     }
     if (t < 0) break;
@@ -333,8 +397,9 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
 #pragma unroll
       for (int i = 0; i < N; ++i) {
         double s = 0.;
+        bool have = false;
 #pragma unroll
-        for (int kk = 0; kk < N; ++kk) s += Fx[kk + N * i] * Vl[L::sym(kk, j)];
+        for (int kk = 0; kk < N; ++kk) TPP_ACC(s, have, M::fx_kind(kk, i), Fx[kk + N * i], Vl[L::sym(kk, j)]);
         A[i + N * j] = s;
       }
     double Qxx[N * N], Qx[N], Qxu[N * U], Quu[U * U], Qu[U], G[U * N];  // G = FuTVxx_p = Fu^T Vxx'
@@ -343,15 +408,17 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
 #pragma unroll
       for (int i = 0; i < N; ++i) {
         double s = 0.;
+        bool have = false;
 #pragma unroll
-        for (int kk = 0; kk < N; ++kk) s += A[i + N * kk] * Fx[kk + N * j];
-        Qxx[i + N * j] = Lxx[i + N * j] + s;
+        for (int kk = 0; kk < N; ++kk) TPP_ACC(s, have, M::fx_kind(kk, j), Fx[kk + N * j], A[i + N * kk]);
+        Qxx[i + N * j] = M::lxx_kind(i, j) ? Lxx[i + N * j] + s : s;
       }
 #pragma unroll
     for (int j = 0; j < N; ++j) {
       double s = 0.;
+      bool have = false;
 #pragma unroll
-      for (int i = 0; i < N; ++i) s += Fx[i + N * j] * Vx[i];
+      for (int i = 0; i < N; ++i) TPP_ACC(s, have, M::fx_kind(i, j), Fx[i + N * j], Vx[i]);
       Qx[j] = Lx[j] + s;
     }
 #pragma unroll
@@ -359,8 +426,9 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
 #pragma unroll
       for (int i = 0; i < U; ++i) {
         double s = 0.;
+        bool have = false;
 #pragma unroll
-        for (int kk = 0; kk < N; ++kk) s += Fu[kk + N * i] * Vl[L::sym(kk, j)];
+        for (int kk = 0; kk < N; ++kk) TPP_ACC(s, have, M::fu_kind(kk, i), Fu[kk + N * i], Vl[L::sym(kk, j)]);
         G[i + U * j] = s;
       }
 #pragma unroll
@@ -368,24 +436,27 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
 #pragma unroll
       for (int i = 0; i < N; ++i) {
         double s = 0.;
+        bool have = false;
 #pragma unroll
-        for (int kk = 0; kk < N; ++kk) s += A[i + N * kk] * Fu[kk + N * j];
-        Qxu[i + N * j] = Lxu[i + N * j] + s;
+        for (int kk = 0; kk < N; ++kk) TPP_ACC(s, have, M::fu_kind(kk, j), Fu[kk + N * j], A[i + N * kk]);
+        Qxu[i + N * j] = M::lxu_kind(i, j) ? Lxu[i + N * j] + s : s;
       }
 #pragma unroll
     for (int j = 0; j < U; ++j)
 #pragma unroll
       for (int i = 0; i < U; ++i) {
         double s = 0.;
+        bool have = false;
 #pragma unroll
-        for (int kk = 0; kk < N; ++kk) s += G[i + U * kk] * Fu[kk + N * j];
-        Quu[i + U * j] = Luu[i + U * j] + s;
+        for (int kk = 0; kk < N; ++kk) TPP_ACC(s, have, M::fu_kind(kk, j), Fu[kk + N * j], G[i + U * kk]);
+        Quu[i + U * j] = M::luu_kind(i, j) ? Luu[i + U * j] + s : s;
       }
 #pragma unroll
     for (int j = 0; j < U; ++j) {
       double s = 0.;
+      bool have = false;
 #pragma unroll
-      for (int i = 0; i < N; ++i) s += Fu[i + N * j] * Vx[i];
+      for (int i = 0; i < N; ++i) TPP_ACC(s, have, M::fu_kind(i, j), Fu[i + N * j], Vx[i]);
       Qu[j] = Lu[j] + s;
       if (has_ureg) Quu[j + U * j] += ureg;
     }
@@ -403,7 +474,7 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
         double lb[U], ub[U], work[box_gains_work_doubles(U)], qinv[U * U];
         int iwork[box_gains_work_ints(U)];
         double kold[L::R_KK];
-        ld_rec<0, L::R_KK / 4>(TPP_REC(c.kk, t, L::R_KK), kold);  // k_[t] of the previous backward pass: the warm start
+        ld_rec<0, L::R_KK / 4>(pkk, kold);  // k_[t] of the previous backward pass: the warm start
 #pragma unroll
         for (int i = 0; i < U; ++i) {
           lb[i] = c.u_lb[(size_t)b * U + i];
@@ -412,7 +483,7 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
         }
         if (box_compute_gains(N, U, Quu, U, Qu, Qxu, N, r + L::XU_U, lb, ub, Kg, U, kg, qinv, c.o, work, iwork)) return 1;
         if (c.quu_inv) {
-          double* qo = c.quu_inv + ((size_t)t * Bp + b) * (U * U);
+          double* qo = c.quu_inv + ((size_t)t * Bp + b) * (U * U);  // box solvers only
 #pragma unroll
           for (int i = 0; i < U * U; ++i) qo[i] = qinv[i];
         }
@@ -497,7 +568,7 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
       dq -= q;
       stop += st;
     }
-    st_rec<0, L::R_KK / 4>(TPP_REC(c.kk, t, L::R_KK), kkrec);
+    st_rec<0, L::R_KK / 4>(pkk, kkrec);
     if (full) {
       double qrec[L::R_Q];
 #pragma unroll
@@ -512,7 +583,7 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
       for (int i = 0; i < N; ++i) qrec[L::Q_X + i] = Qx[i];
 #pragma unroll
       for (int i = 0; i < U; ++i) qrec[L::Q_U + i] = Qu[i];
-      st_rec<0, L::R_Q / 4>(TPP_REC(c.q, t, L::R_Q), qrec);
+      st_rec<0, L::R_Q / 4>(c.q + ((size_t)t * Bp + b) * L::R_Q, qrec);
     }
     // Vx = Qx + K^T Quuk - 2 K^T Qu ; Vxx = Qxx - Qxu K   (ddp.cpp:223-233)
 #pragma unroll
@@ -554,13 +625,32 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
         if (!(av <= nrm)) nrm = av;
       }
     if (raise_if_nan(nrm)) return 1;  // ddp.cpp:249-251
+    if constexpr (GAPS) {
 #pragma unroll
-    for (int i = 0; i < L::R_XU; ++i) rp[i] = r[i];
+      for (int i = 0; i < L::R_XU; ++i) rp[i] = r[i];
+    }
+    pxu -= sxu;
+    pv -= sv;
+    pkk -= skk;
+  }
+  if (recalc) {  // what the gap sectors of this buffer hold now
+    if (is_feasible)
+      fszero |= 1 << cur;
+    else
+      fszero &= ~(1 << cur);
   }
   dg_out = dg;
   dq_out = dq;
   stop_out = stop;
   return 0;
+}
+template <class M, bool BOX = false>
+TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, bool recalc, bool is_feasible,
+                                bool was_feasible, double xreg, double ureg, double& dg_out, double& dq_out,
+                                double& stop_out, int& fszero) {
+  (void)was_feasible;
+  if (is_feasible) return tpp_backward_impl<M, BOX, false>(c, m, b, cur, recalc, xreg, ureg, dg_out, dq_out, stop_out, fszero);
+  return tpp_backward_impl<M, BOX, true>(c, m, b, cur, recalc, xreg, ureg, dg_out, dq_out, stop_out, fszero);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -568,19 +658,21 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
 // branch with xs_try[0] = x0) fused with SolverFDDP::expectedImprovement's gap reduction
 // dv = -sum_t fs_t^T Vxx_t (xs_t - xs_try_t) = sum_t w_t^T dx_t (fddp.cpp:107-124).
 // Reads the candidate records XU[cur], writes the trial records XU[cur^1]. Returns 0, or 1 = "forward_error".
-template <class M, bool BOX = false>
-TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, int cur, double alpha, bool is_feasible,
-                               double& cost_try_out, double& dv_out) {
+// GAPS = the rollout may be open (FDDP / box-DDP from an infeasible candidate): only that instantiation reads the gaps
+// and w = Vxx fs; a rollout from a feasible candidate moves x, u, K, k only
+template <class M, bool BOX, bool GAPS>
+TPP_SWEEP_ATTR int tpp_forward_impl(const TppCtx& c, const M& m, int b, int cur, double alpha, bool is_feasible,
+                                    double& cost_try_out, double& dv_out) {
   typedef TppLayout<M> L;
   constexpr int N = M::NX, U = M::NU;
   constexpr int SR = L::R_XU / 4, SK = L::R_KK / 4, SW = rup4(N) / 4;
   const int Bp = c.Bp, T = c.T;
   const bool fddp = c.fddp != 0;
-  const bool closed = !fddp || is_feasible || (alpha == 1.);
-  const bool use_w = fddp && !is_feasible;
+  const bool closed = !GAPS || !fddp || is_feasible || (alpha == 1.);
+  const bool use_w = GAPS && fddp && !is_feasible;
   const double am1 = alpha - 1.;
   // SolverBoxDDP::forwardPass keeps the gap of the TERMINAL node only (box-ddp.cpp:121-125)
-  const bool term_open = BOX && !fddp && !(is_feasible || (alpha == 1.));
+  const bool term_open = GAPS && BOX && !fddp && !(is_feasible || (alpha == 1.));
   bool clamp = false;
   double ulb[U], uub[U];
   if constexpr (BOX) {
@@ -591,59 +683,77 @@ TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, int cur, doub
       uub[i] = c.u_ub[(size_t)b * U + i];
     }
   }
-  const double* __restrict__ xu = c.xu[cur];
-  double* __restrict__ xt_ = c.xu[cur ^ 1];
+  constexpr int SXA = L::XU_F / 4;
+  const bool need_fs = !closed || term_open;  // the gaps are read only by an open rollout
+  const size_t sxu = (size_t)Bp * L::R_XU, skk = (size_t)Bp * L::R_KK, sv = (size_t)Bp * L::R_V;
+  const double* __restrict__ pxu = c.xu[cur] + (size_t)b * L::R_XU;  // candidate record of node t + 1 (prefetched)
+  double* __restrict__ pxt = c.xu[cur ^ 1] + (size_t)b * L::R_XU;    // trial record of node t
+  const double* __restrict__ pkk = c.kk + (size_t)b * L::R_KK;
+  const double* __restrict__ pv = c.v + (size_t)b * L::R_V;
   double cost_try = 0., dv = 0.;
   double xn[N], xt[N], dx[N];
   // software prefetch of node t+1's inputs (none of them depends on the rollout recursion)
-  double qa[L::R_XU], qk[L::R_KK], qw[4 * SW];
+  constexpr int RW = GAPS ? L::R_XU : L::XU_F;
+  double qa[RW], qk[L::R_KK], qw[4 * SW];
 #pragma unroll
   for (int i = 0; i < 4 * SW; ++i) qw[i] = 0.;
-  auto fetch = [&](int t) {
-    ld_rec<0, SR>(TPP_REC(xu, t, L::R_XU), qa);
-    if (use_w) ld_rec<0, SW>(TPP_REC(c.v, t, L::R_V), qw);
-    if (t < T) ld_rec<0, SK>(TPP_REC(c.kk, t, L::R_KK), qk);
-  };
-  auto prefetch = [&](int t) {
-    pf_rec<0, SR>(TPP_REC(xu, t, L::R_XU));
-    if (use_w) pf_rec<0, SW>(TPP_REC(c.v, t, L::R_V));
-    if (t < T) pf_rec<0, SK>(TPP_REC(c.kk, t, L::R_KK));
+#pragma unroll
+  for (int i = 0; i < RW; ++i) qa[i] = 0.;
+  auto fetch = [&](int t) {  // node t's inputs; the pointers stand on node t
+    ld_rec<0, SXA>(pxu, qa);
+    if constexpr (GAPS) {
+      if (need_fs) ld_rec<SXA, SR>(pxu, qa);
+      if (use_w) ld_rec<0, SW>(pv, qw);
+    }
+    if (t < T) ld_rec<0, SK>(pkk, qk);
   };
 #pragma unroll
   for (int i = 0; i < N; ++i) xn[i] = c.x0[(size_t)i * Bp + b];
   fetch(0);
   for (int t = 0; t <= T; ++t) {
-    double ca[L::R_XU], ck[L::R_KK], cw[N], o[L::R_XU];
+    double ca[RW], ck[L::R_KK], cw[N], o[4 * SXA];
 #pragma unroll
-    for (int i = 0; i < L::R_XU; ++i) ca[i] = qa[i];
+    for (int i = 0; i < RW; ++i) ca[i] = qa[i];
 #pragma unroll
     for (int i = 0; i < L::R_KK; ++i) ck[i] = qk[i];
 #pragma unroll
     for (int i = 0; i < N; ++i) cw[i] = qw[L::V_W + i];
+    pxu += sxu;
+    pkk += skk;
+    pv += sv;
     if (t < T) fetch(t + 1);
-    if (t + TPP_PF_DIST <= T) prefetch(t + TPP_PF_DIST);
+    if (t + TPP_PF_DIST <= T) {  // node t + TPP_PF_DIST into L2
+      pf_rec<0, SXA>(pxu + (TPP_PF_DIST - 1) * sxu);
+      if constexpr (GAPS) {
+        if (need_fs) pf_rec<SXA, SR>(pxu + (TPP_PF_DIST - 1) * sxu);
+        if (use_w) pf_rec<0, SW>(pv + (TPP_PF_DIST - 1) * sv);
+      }
+      if (t + TPP_PF_DIST < T) pf_rec<0, SK>(pkk + (TPP_PF_DIST - 1) * skk);
+    }
     if (closed && !(term_open && t == T)) {
 #pragma unroll
       for (int i = 0; i < N; ++i) xt[i] = xn[i];
-    } else {
+    } else if constexpr (GAPS) {
 #pragma unroll
       for (int i = 0; i < N; ++i) xt[i] = xn[i] + ca[L::XU_F + i] * am1;  // integrate(xnext, fs*(a-1))
     }
 #pragma unroll
-    for (int i = 0; i < L::R_XU; ++i) o[i] = 0.;
+    for (int i = 0; i < 4 * SXA; ++i) o[i] = 0.;
 #pragma unroll
     for (int i = 0; i < N; ++i) {
       dx[i] = xt[i] - ca[L::XU_X + i];
       o[L::XU_X + i] = xt[i];
     }
-    if (use_w) {
-      double s = 0.;
+    if constexpr (GAPS) {
+      if (use_w) {
+        double s = 0.;
 #pragma unroll
-      for (int i = 0; i < N; ++i) s += cw[i] * dx[i];
-      dv += s;
+        for (int i = 0; i < N; ++i) s += cw[i] * dx[i];
+        dv += s;
+      }
     }
     if (t == T) {
-      st_rec<0, SR>(TPP_REC(xt_, t, L::R_XU), o);
+      st_rec<0, SXA>(pxt, o);
       break;
     }
     double* u = o + L::XU_U;
@@ -655,8 +765,10 @@ TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, int cur, doub
       u[i] = ca[L::XU_U + i] - ck[L::KK_k + i] * alpha - s;
       if (BOX && clamp) u[i] = fmin(fmax(u[i], ulb[i]), uub[i]);  // cwiseMax(lb).cwiseMin(ub)
     }
-    st_rec<0, SR>(TPP_REC(xt_, t, L::R_XU), o);
-    cost_try += m.calc(xt, u, xn);
+    // calc leaves aux (what the next backward pass reuses) in the trial record
+    cost_try += m.calc(xt, u, xn, o + L::XU_A);
+    st_rec<0, SXA>(pxt, o);
+    pxt += sxu;
     double nrm = 0.;
 #pragma unroll
     for (int i = 0; i < N; ++i) {
@@ -671,12 +783,18 @@ TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, int cur, doub
     for (int i = 0; i < U; ++i) u0[i] = 0.;
     M mt;
     mt.load(c.tparams);
-    cost_try += mt.calc(xt, u0, xn);
+    cost_try += mt.cost(xt, u0);
   }
   if (raise_if_nan(cost_try)) return 1;
   cost_try_out = cost_try;
   dv_out = dv;
   return 0;
+}
+template <class M, bool BOX = false>
+TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, int cur, double alpha, bool is_feasible,
+                               double& cost_try_out, double& dv_out) {
+  if (!is_feasible && (c.fddp != 0 || BOX)) return tpp_forward_impl<M, BOX, true>(c, m, b, cur, alpha, is_feasible, cost_try_out, dv_out);
+  return tpp_forward_impl<M, BOX, false>(c, m, b, cur, alpha, is_feasible, cost_try_out, dv_out);
 }
 
 // acceptance tests of the line search (ddp.cpp:84-93 / fddp.cpp:64-80)
@@ -719,6 +837,7 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
   double steplength = TPP_S(S_STEP), dV = TPP_S(S_DV), dVexp = TPP_S(S_DVEXP), cost_try = TPP_S(S_COST_TRY);
   double dg = 0., dq = 0.;
   int nbwd = 0, nfwd = 0, nrec = 0, converged = 0, iter = 0;
+  int fszero = 0;  // what the gap sectors of the two candidate buffers hold (tpp_backward)
   bool recalc = true, need_gaps = true, done = false;
   if (!first) {  // resume
     feas = TPP_I(I_FEAS) != 0;
@@ -734,6 +853,7 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
     const int lp = TPP_I(I_LOOP);
     recalc = (lp & 1) != 0;
     need_gaps = (lp & 2) != 0;
+    fszero = (lp >> 2) & 3;
   }
   int budget = chunk > 0 ? chunk : maxiter + 1;
   bool paused = false;
@@ -750,7 +870,7 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
     if (recalc) need_gaps = true;
     while (true) {  // computeDirection with regularisation retry (ddp.cpp:55-68)
       if (need_gaps) fsbuf = cur;
-      const int st = tpp_backward<M, BOX>(c, m, b, cur, need_gaps, feas, wasfeas, xreg, ureg, dg, dq, stop);
+      const int st = tpp_backward<M, BOX>(c, m, b, cur, need_gaps, feas, wasfeas, xreg, ureg, dg, dq, stop, fszero);
       ++nbwd;
       if (st == 0) {
         need_gaps = false;
@@ -841,7 +961,7 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
   TPP_I(I_NREC) = nrec;
   TPP_I(I_NBWD) = nbwd;
   TPP_I(I_NFWD) = nfwd;
-  TPP_I(I_LOOP) = (recalc ? 1 : 0) | (need_gaps ? 2 : 0);
+  TPP_I(I_LOOP) = (recalc ? 1 : 0) | (need_gaps ? 2 : 0) | (fszero << 2);
   TPP_I(I_FINISHED) = paused ? 0 : 1;
 }
 
@@ -900,7 +1020,9 @@ __global__ void __launch_bounds__(64) tpp_direction_kernel(const __grid_constant
     TPP_I(I_FSBUF) = cur;
   }
   double dg = 0., dq = 0., stop = 0.;
-  const int st = tpp_backward<M, BOX>(c, m, b, cur, recalc != 0, feas, wasfeas, TPP_S(S_XREG), TPP_S(S_UREG), dg, dq, stop);
+  int fszero = 0;  // step-wise call: a feasible candidate always zero-fills its gap sectors
+  const int st = tpp_backward<M, BOX>(c, m, b, cur, recalc != 0, feas, wasfeas, TPP_S(S_XREG), TPP_S(S_UREG), dg, dq, stop,
+                                      fszero);
   TPP_I(I_BSTATUS) = st;
   if (st == 0) {
     TPP_S(S_DG) = dg;

@@ -12,9 +12,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libcrocoddyl_b200.so")
-# per-source extra flags. tpp_backend.cu: the thread-per-problem solve kernel must stay <= 128 registers so
-# that 65,536 problems are resident in ONE wave (8 blocks x 64 threads per SM; measured: 144 registers already falls back to two waves).
-EXTRA = {"tpp_backend.cu": ["-maxrregcount=128"]}
+# per-source extra flags (none: the register budget of the thread-per-problem solve kernel — 128, so that 65,536 problems
+# are resident in ONE wave — is set by its __launch_bounds__, and its tail instantiation deliberately has none)
+EXTRA = {}
 SOURCES = ["cta_arm7.cu", "cta_arm4.cu", "cta_arm2.cu", "cta_backend.cu", "tpp_backend.cu", "capi.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-Xcompiler", "-fvisibility=hidden"]

@@ -98,6 +98,37 @@ __device__ __forceinline__ void pf_rec(const double* p) {
   for (int s = S0; s < S1; ++s) prefetch_l2(p + 4 * s);
 }
 
+// Per-thread staging area in shared memory for the NEXT node's records: cp.async (LDGSTS, 16 bytes per request) moves
+// them from L2 while the current node is computed, without holding them in registers (under the 128-register cap of
+// the one-wave solve kernel a register prefetch is spilled as soon as it lands — ncu: 30 % of all stall samples on the
+// spill store and the first move of the prefetched record). Layout [buffer][16-byte chunk][thread]: the lanes of a warp
+// touch consecutive 16-byte words (no bank conflicts); groups are per thread, so diverged lanes stage independently.
+#define TPP_BLOCK 64
+#define TPP_STG_CHUNKS 12  // x,u,aux (4) + K,k (4) + fs (2) + w (2) for the unicycle; checked per model below
+struct TppStage {
+  double2 s[2][TPP_STG_CHUNKS][TPP_BLOCK];
+};
+// sectors [0, NSEC) of the record at g -> chunks [C0, C0 + 2 NSEC) of buffer buf
+template <int C0, int NSEC>
+__device__ __forceinline__ void stg_issue(TppStage& S, int buf, const double* g) {
+#pragma unroll
+  for (int k = 0; k < 2 * NSEC; ++k) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(&S.s[buf][C0 + k][threadIdx.x]);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(g + 2 * k) : "memory");
+  }
+}
+__device__ __forceinline__ void stg_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void stg_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+template <int C0, int NSEC>
+__device__ __forceinline__ void stg_read(const TppStage& S, int buf, double* o) {
+#pragma unroll
+  for (int k = 0; k < 2 * NSEC; ++k) {
+    const double2 v = S.s[buf][C0 + k][threadIdx.x];
+    o[2 * k] = v.x;
+    o[2 * k + 1] = v.y;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // ActionModelUnicycle (reference: include/crocoddyl/core/actions/unicycle.hxx:13-73, unicycle.hpp:78-80)
 struct UnicycleModel {
@@ -194,7 +225,6 @@ struct UnicycleModel {
   }
 };
 
-#define TPP_BLOCK 64
 #ifdef TPP_NOINLINE
 #define TPP_SWEEP_ATTR __device__ __noinline__
 #else
@@ -264,8 +294,8 @@ TPP_SWEEP_ATTR double tpp_calc_pass(const TppCtx& c, const M& m, int b, double* 
 // GAPS = !is_feasible: the feasible instantiation carries no gap / w arithmetic and no record of node t + 1 at all
 // (most sweeps of a solve run on a feasible candidate)
 template <class M, bool BOX, bool GAPS>
-TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, int b, int cur, bool recalc, double xreg, double ureg,
-                                     double& dg_out, double& dq_out, double& stop_out, int& fszero) {
+TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, TppStage& stg, int b, int cur, bool recalc, double xreg,
+                                     double ureg, double& dg_out, double& dq_out, double& stop_out, int& fszero) {
   constexpr bool is_feasible = !GAPS;
   typedef TppLayout<M> L;
   constexpr int N = M::NX, U = M::NU, NL = L::NL;
@@ -284,21 +314,27 @@ TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, int b, int cur
   const bool zero_fs = !GAPS && recalc && !((fszero >> cur) & 1);
   double Vl[NL], Vx[N];
   double Fx[N * N], Fu[N * U], Lx[N], Lu[U], Lxx[N * N], Lxu[N * U], Luu[U * U], xn[N];
-  // records in registers: rp = node t + 1 (x and the gaps: GAPS only), r = node t, rq = node t - 1 (prefetched)
+  // records: rp = node t + 1 (x and the gaps: GAPS only) and r = node t in registers; node t - 1 is on its way into
+  // the shared-memory staging buffer while node t is computed
   constexpr int RW = GAPS ? L::R_XU : L::XU_F;  // the feasible instantiation never holds a gap sector
-  double rp[L::R_XU], r[RW], rq[RW];
+  constexpr int CF = 2 * SXA;                    // staging chunk of the gap sector(s)
+  static_assert(2 * SR <= TPP_STG_CHUNKS, "staging area too small for this model");
+  double rp[L::R_XU], r[RW];
 #pragma unroll
   for (int i = 0; i < L::R_XU; ++i) rp[i] = 0.;
 #pragma unroll
-  for (int i = 0; i < RW; ++i) rq[i] = 0.;
-  // terminal node (ddp.cpp:181-187): u = unone_ = 0 (action-base.hxx:27-37)
-  ld_rec<0, SXA>(pxu, rp);
-  ld_rec<0, SXA>(pxu - sxu, rq);
+  for (int i = 0; i < RW; ++i) r[i] = 0.;
+  int buf = 0;
+  stg_wait();  // nothing of an earlier sweep (one that returned on an error) may still be landing in the staging area
+  // node T - 1 into the staging buffer, then the terminal node (ddp.cpp:181-187): u = unone_ = 0 (action-base.hxx:27-37)
+  stg_issue<0, SXA>(stg, buf, pxu - sxu);
   if constexpr (GAPS) {
-    if (load_fs) {
-      ld_rec<SXA, SR>(pxu, rp);
-      ld_rec<SXA, SR>(pxu - sxu, rq);
-    }
+    if (load_fs) stg_issue<CF, SR - SXA>(stg, buf, pxu - sxu + L::XU_F);
+  }
+  stg_commit();
+  ld_rec<0, SXA>(pxu, rp);
+  if constexpr (GAPS) {
+    if (load_fs) ld_rec<SXA, SR>(pxu, rp);
   }
   {
     double u0[U];
@@ -317,15 +353,20 @@ TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, int b, int cur
 
   for (int t = T - 1; t >= -1; --t) {
     if (t >= 0) {
-#pragma unroll
-      for (int i = 0; i < RW; ++i) r[i] = rq[i];
-      // software prefetch: node t-1's record is requested before node t's dependent Riccati chain starts,
-      // node t-1-TPP_PF_DIST's record is pulled into L2
+      stg_wait();
+      stg_read<0, SXA>(stg, buf, r);
+      if constexpr (GAPS) {
+        if (load_fs) stg_read<CF, SR - SXA>(stg, buf, r + L::XU_F);
+      }
+      buf ^= 1;
+      // node t-1's record is requested (cp.async into the other staging buffer) before node t's dependent Riccati
+      // chain starts, node t-1-TPP_PF_DIST's record is pulled into L2
       if (t > 0) {
-        ld_rec<0, SXA>(pxu - 2 * sxu, rq);
+        stg_issue<0, SXA>(stg, buf, pxu - 2 * sxu);
         if constexpr (GAPS) {
-          if (load_fs) ld_rec<SXA, SR>(pxu - 2 * sxu, rq);
+          if (load_fs) stg_issue<CF, SR - SXA>(stg, buf, pxu - 2 * sxu + L::XU_F);
         }
+        stg_commit();
       }
       if (t > TPP_PF_DIST) {
         pf_rec<0, SXA>(pxu - (2 + TPP_PF_DIST) * sxu);
@@ -645,12 +686,12 @@ TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, int b, int cur
   return 0;
 }
 template <class M, bool BOX = false>
-TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, bool recalc, bool is_feasible,
+TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, TppStage& stg, int b, int cur, bool recalc, bool is_feasible,
                                 bool was_feasible, double xreg, double ureg, double& dg_out, double& dq_out,
                                 double& stop_out, int& fszero) {
   (void)was_feasible;
-  if (is_feasible) return tpp_backward_impl<M, BOX, false>(c, m, b, cur, recalc, xreg, ureg, dg_out, dq_out, stop_out, fszero);
-  return tpp_backward_impl<M, BOX, true>(c, m, b, cur, recalc, xreg, ureg, dg_out, dq_out, stop_out, fszero);
+  if (is_feasible) return tpp_backward_impl<M, BOX, false>(c, m, stg, b, cur, recalc, xreg, ureg, dg_out, dq_out, stop_out, fszero);
+  return tpp_backward_impl<M, BOX, true>(c, m, stg, b, cur, recalc, xreg, ureg, dg_out, dq_out, stop_out, fszero);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -661,8 +702,8 @@ TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, int b, int cur, boo
 // GAPS = the rollout may be open (FDDP / box-DDP from an infeasible candidate): only that instantiation reads the gaps
 // and w = Vxx fs; a rollout from a feasible candidate moves x, u, K, k only
 template <class M, bool BOX, bool GAPS>
-TPP_SWEEP_ATTR int tpp_forward_impl(const TppCtx& c, const M& m, int b, int cur, double alpha, bool is_feasible,
-                                    double& cost_try_out, double& dv_out) {
+TPP_SWEEP_ATTR int tpp_forward_impl(const TppCtx& c, const M& m, TppStage& stg, int b, int cur, double alpha,
+                                    bool is_feasible, double& cost_try_out, double& dv_out) {
   typedef TppLayout<M> L;
   constexpr int N = M::NX, U = M::NU;
   constexpr int SR = L::R_XU / 4, SK = L::R_KK / 4, SW = rup4(N) / 4;
@@ -692,20 +733,21 @@ TPP_SWEEP_ATTR int tpp_forward_impl(const TppCtx& c, const M& m, int b, int cur,
   const double* __restrict__ pv = c.v + (size_t)b * L::R_V;
   double cost_try = 0., dv = 0.;
   double xn[N], xt[N], dx[N];
-  // software prefetch of node t+1's inputs (none of them depends on the rollout recursion)
+  // node t+1's inputs (none of them depends on the rollout recursion) travel into the shared-memory staging buffer
+  // while node t is computed: chunks [0, CK) = x,u,aux  [CK, CFS) = K,k  then the gaps and w (GAPS only)
   constexpr int RW = GAPS ? L::R_XU : L::XU_F;
-  double qa[RW], qk[L::R_KK], qw[4 * SW];
-#pragma unroll
-  for (int i = 0; i < 4 * SW; ++i) qw[i] = 0.;
-#pragma unroll
-  for (int i = 0; i < RW; ++i) qa[i] = 0.;
+  constexpr int CK = 2 * SXA, CFS = CK + 2 * SK, CW = CFS + 2 * (SR - SXA);
+  static_assert(CW + 2 * SW <= TPP_STG_CHUNKS, "staging area too small for this model");
+  int buf = 0;
+  stg_wait();  // nothing of an earlier sweep may still be landing in the staging area
   auto fetch = [&](int t) {  // node t's inputs; the pointers stand on node t
-    ld_rec<0, SXA>(pxu, qa);
+    stg_issue<0, SXA>(stg, buf, pxu);
     if constexpr (GAPS) {
-      if (need_fs) ld_rec<SXA, SR>(pxu, qa);
-      if (use_w) ld_rec<0, SW>(pv, qw);
+      if (need_fs) stg_issue<CFS, SR - SXA>(stg, buf, pxu + L::XU_F);
+      if (use_w) stg_issue<CW, SW>(stg, buf, pv);
     }
-    if (t < T) ld_rec<0, SK>(pkk, qk);
+    if (t < T) stg_issue<CK, SK>(stg, buf, pkk);
+    stg_commit();
   };
 #pragma unroll
   for (int i = 0; i < N; ++i) xn[i] = c.x0[(size_t)i * Bp + b];
@@ -713,11 +755,22 @@ TPP_SWEEP_ATTR int tpp_forward_impl(const TppCtx& c, const M& m, int b, int cur,
   for (int t = 0; t <= T; ++t) {
     double ca[RW], ck[L::R_KK], cw[N], o[4 * SXA];
 #pragma unroll
-    for (int i = 0; i < RW; ++i) ca[i] = qa[i];
+    for (int i = 0; i < RW; ++i) ca[i] = 0.;
 #pragma unroll
-    for (int i = 0; i < L::R_KK; ++i) ck[i] = qk[i];
+    for (int i = 0; i < N; ++i) cw[i] = 0.;
+    stg_wait();
+    stg_read<0, SXA>(stg, buf, ca);
+    if (t < T) stg_read<CK, SK>(stg, buf, ck);
+    if constexpr (GAPS) {
+      if (need_fs) stg_read<CFS, SR - SXA>(stg, buf, ca + L::XU_F);
+      if (use_w) {
+        double w4[4 * SW];
+        stg_read<CW, SW>(stg, buf, w4);
 #pragma unroll
-    for (int i = 0; i < N; ++i) cw[i] = qw[L::V_W + i];
+        for (int i = 0; i < N; ++i) cw[i] = w4[L::V_W + i];
+      }
+    }
+    buf ^= 1;
     pxu += sxu;
     pkk += skk;
     pv += sv;
@@ -791,10 +844,10 @@ TPP_SWEEP_ATTR int tpp_forward_impl(const TppCtx& c, const M& m, int b, int cur,
   return 0;
 }
 template <class M, bool BOX = false>
-TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, int b, int cur, double alpha, bool is_feasible,
+TPP_SWEEP_ATTR int tpp_forward(const TppCtx& c, const M& m, TppStage& stg, int b, int cur, double alpha, bool is_feasible,
                                double& cost_try_out, double& dv_out) {
-  if (!is_feasible && (c.fddp != 0 || BOX)) return tpp_forward_impl<M, BOX, true>(c, m, b, cur, alpha, is_feasible, cost_try_out, dv_out);
-  return tpp_forward_impl<M, BOX, false>(c, m, b, cur, alpha, is_feasible, cost_try_out, dv_out);
+  if (!is_feasible && (c.fddp != 0 || BOX)) return tpp_forward_impl<M, BOX, true>(c, m, stg, b, cur, alpha, is_feasible, cost_try_out, dv_out);
+  return tpp_forward_impl<M, BOX, false>(c, m, stg, b, cur, alpha, is_feasible, cost_try_out, dv_out);
 }
 
 // acceptance tests of the line search (ddp.cpp:84-93 / fddp.cpp:64-80)
@@ -818,10 +871,10 @@ __device__ inline bool accept_step(const SolverOpts& o, bool fddp, bool is_feasi
 // host compacts the unfinished problems into `list` (tpp_compact_*), so that a launch only spends lanes on OCPs that
 // still iterate: each OCP has its own iteration count, and without compaction one slow lane keeps its whole warp
 // alive (ncu, profiles/README.md: 19 % of the warp slots active at B = 65,536).
-template <class M, bool BOX = false>
-__global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, int is_feasible0, double reginit, int chunk,
-                                 int first, const int* __restrict__ list, const int* __restrict__ nactive, int b_lo,
-                                 int b_hi) {
+template <class M, bool BOX>
+__device__ __forceinline__ void tpp_solve_body(const TppCtx& c, TppStage& stg, int maxiter, int is_feasible0, double reginit,
+                                               int chunk, int first, const int* __restrict__ list,
+                                               const int* __restrict__ nactive, int b_lo, int b_hi) {
   // a launch owns the problems [b_lo, b_hi) (slices of the batch on different streams, TppBackend::solve_pipelined)
   const int gid = b_lo + blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= (list ? *nactive : b_hi)) return;
@@ -870,7 +923,7 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
     if (recalc) need_gaps = true;
     while (true) {  // computeDirection with regularisation retry (ddp.cpp:55-68)
       if (need_gaps) fsbuf = cur;
-      const int st = tpp_backward<M, BOX>(c, m, b, cur, need_gaps, feas, wasfeas, xreg, ureg, dg, dq, stop, fszero);
+      const int st = tpp_backward<M, BOX>(c, m, stg, b, cur, need_gaps, feas, wasfeas, xreg, ureg, dg, dq, stop, fszero);
       ++nbwd;
       if (st == 0) {
         need_gaps = false;
@@ -894,7 +947,7 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
     for (int a = 0; a < c.o.nalphas; ++a) {
       steplength = c.o.alphas[a];
       double dv = 0.;
-      const int st = tpp_forward<M, BOX>(c, m, b, cur, steplength, feas, cost_try, dv);
+      const int st = tpp_forward<M, BOX>(c, m, stg, b, cur, steplength, feas, cost_try, dv);
       ++nfwd;
       if (st) continue;
       dV = cost - cost_try;
@@ -964,6 +1017,25 @@ __global__ void tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, 
   TPP_I(I_LOOP) = (recalc ? 1 : 0) | (need_gaps ? 2 : 0) | (fszero << 2);
   TPP_I(I_FINISHED) = paused ? 0 : 1;
 }
+// The whole batch in ONE wave: 8 blocks of 64 threads per SM = 128 registers per thread (measured: with 144 registers
+// the last blocks of a 65,536-problem batch wait for a second wave behind the slowest problems).
+template <class M, bool BOX = false>
+__global__ void __launch_bounds__(TPP_BLOCK, 8)
+    tpp_solve_kernel(const __grid_constant__ TppCtx c, int maxiter, int is_feasible0, double reginit, int chunk, int first,
+                     const int* __restrict__ list, const int* __restrict__ nactive, int b_lo, int b_hi) {
+  __shared__ TppStage stg;
+  tpp_solve_body<M, BOX>(c, stg, maxiter, is_feasible0, reginit, chunk, first, list, nactive, b_lo, b_hi);
+}
+// The same loop for the TAIL of a batch (the few problems that are still iterating when most have returned, compacted
+// into `list`): occupancy is irrelevant there — each warp runs alone on its scheduler at the speed of its own dependent
+// chain — so this instantiation takes all the registers it wants (no spills on the chain) and one warp per block.
+template <class M, bool BOX = false>
+__global__ void __launch_bounds__(TPP_BLOCK, 2)
+    tpp_solve_tail_kernel(const __grid_constant__ TppCtx c, int maxiter, int is_feasible0, double reginit, int chunk,
+                          int first, const int* __restrict__ list, const int* __restrict__ nactive, int b_lo, int b_hi) {
+  __shared__ TppStage stg;
+  tpp_solve_body<M, BOX>(c, stg, maxiter, is_feasible0, reginit, chunk, first, list, nactive, b_lo, b_hi);
+}
 
 // Ordered compaction of the unfinished problems (keeps neighbouring OCPs in neighbouring lanes):
 //   pass 1: counts[blk] = unfinished problems among the 1024 of block blk
@@ -1008,6 +1080,7 @@ __global__ void __launch_bounds__(1024) tpp_compact_scatter_kernel(const int* __
 // always runs with iter_ == 0, so problem_->calc is evaluated) + backwardPass.
 template <class M, bool BOX = false>
 __global__ void __launch_bounds__(64) tpp_direction_kernel(const __grid_constant__ TppCtx c, int recalc) {
+  __shared__ TppStage stg;
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= c.B) return;
   const int Bp = c.Bp;
@@ -1021,7 +1094,7 @@ __global__ void __launch_bounds__(64) tpp_direction_kernel(const __grid_constant
   }
   double dg = 0., dq = 0., stop = 0.;
   int fszero = 0;  // step-wise call: a feasible candidate always zero-fills its gap sectors
-  const int st = tpp_backward<M, BOX>(c, m, b, cur, recalc != 0, feas, wasfeas, TPP_S(S_XREG), TPP_S(S_UREG), dg, dq, stop,
+  const int st = tpp_backward<M, BOX>(c, m, stg, b, cur, recalc != 0, feas, wasfeas, TPP_S(S_XREG), TPP_S(S_UREG), dg, dq, stop,
                                       fszero);
   TPP_I(I_BSTATUS) = st;
   if (st == 0) {
@@ -1038,6 +1111,7 @@ __global__ void __launch_bounds__(64) tpp_direction_kernel(const __grid_constant
 // tryStep(alpha) (ddp.cpp:127-130)
 template <class M, bool BOX = false>
 __global__ void __launch_bounds__(64) tpp_trystep_kernel(const __grid_constant__ TppCtx c, double alpha) {
+  __shared__ TppStage stg;
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= c.B) return;
   const int Bp = c.Bp;
@@ -1046,7 +1120,7 @@ __global__ void __launch_bounds__(64) tpp_trystep_kernel(const __grid_constant__
   const int cur = TPP_I(I_CUR);
   const bool feas = TPP_I(I_FEAS) != 0;
   double cost_try = 0., dv = 0.;
-  const int st = tpp_forward<M, BOX>(c, m, b, cur, alpha, feas, cost_try, dv);
+  const int st = tpp_forward<M, BOX>(c, m, stg, b, cur, alpha, feas, cost_try, dv);
   TPP_I(I_FSTATUS) = st;
   if (st == 0) {
     TPP_S(S_COST_TRY) = cost_try;

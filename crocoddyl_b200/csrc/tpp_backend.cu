@@ -46,6 +46,11 @@ struct TppBackend : Backend {
     c.u_ub = p->d_uub;
     c.has_limits = p->d_haslim;
     c.x0 = alloc((size_t)N * c.Bp);
+    // 8 resident blocks of the solve kernel per SM (the whole batch in one wave) need 8 x 24.6 KB of staging area
+    CGX_CUDA(cudaFuncSetAttribute(tpp_solve_kernel<M, false>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                  cudaSharedmemCarveoutMaxShared));
+    CGX_CUDA(cudaFuncSetAttribute(tpp_solve_kernel<M, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                  cudaSharedmemCarveoutMaxShared));
     x0_changed();
   }
   ~TppBackend() override {
@@ -144,6 +149,12 @@ struct TppBackend : Backend {
   // 65.5 ms. The loop is bound by the dependent instruction chain of each OCP (0.3 ms per iteration for a lone warp)
   // and by instruction issue while all OCPs are alive, not by idle lanes, and compaction scatters the lanes' records
   // over DRAM pages. So the default stays ONE launch (0); CROCODDYL_B200_TPP_CHUNK=<n> enables the chunked path.
+  // iteration after which the unfinished problems of a large batch are compacted and handed to the tail kernel
+  // (0 = never). CROCODDYL_B200_TPP_TAIL_AT overrides (development knob).
+  int tail_iter() const {
+    const char* e = getenv("CROCODDYL_B200_TPP_TAIL_AT");
+    return e ? atoi(e) : 40;
+  }
   int chunk_iters() const {
     const char* e = getenv("CROCODDYL_B200_TPP_CHUNK");
     return e ? atoi(e) : 0;
@@ -248,18 +259,20 @@ struct TppBackend : Backend {
   void solve(int maxiter, int is_feasible, double reginit) override {
     c.o = o;
     const int chunk = chunk_iters();
+    const int tail_at = tail_iter();
     CGX_CUDA(cudaEventRecord(ev[1], stream));
-    if (chunk <= 0 || maxiter <= chunk) {
-      TPP_LAUNCH_BOX(tpp_solve_kernel, (nblocks(), TPP_BLOCK, 0, stream), c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr, 0, c.B);
-      ++last_launches;
-    } else {
-      const int cblocks = (c.B + 1023) / 1024;
+    auto compaction = [&](int*& d_counts, int*& d_nactive, int& cblocks) {
+      cblocks = (c.B + 1023) / 1024;
       if (!d_list) {
         d_list = dalloc<int>((size_t)c.Bp + cblocks + 1);
         allocs.push_back(d_list);
       }
-      int* d_counts = d_list + c.Bp;
-      int* d_nactive = d_counts + cblocks;
+      d_counts = d_list + c.Bp;
+      d_nactive = d_counts + cblocks;
+    };
+    if (chunk > 0 && maxiter > chunk) {
+      int *d_counts, *d_nactive, cblocks;
+      compaction(d_counts, d_nactive, cblocks);
       const int* fin = c.iscal + (size_t)I_FINISHED * c.Bp;
       TPP_LAUNCH_BOX(tpp_solve_kernel, (nblocks(), TPP_BLOCK, 0, stream), c, maxiter, is_feasible, reginit, chunk, 1, nullptr, nullptr, 0, c.B);
       ++last_launches;
@@ -269,6 +282,23 @@ struct TppBackend : Backend {
         TPP_LAUNCH_BOX(tpp_solve_kernel, (nblocks(), TPP_BLOCK, 0, stream), c, maxiter, is_feasible, reginit, chunk, 0, d_list, d_nactive, 0, c.B);
         last_launches += 3;
       }
+    } else if (tail_at > 0 && maxiter > tail_at && c.B >= 4096) {
+      // Two regimes of a large batch: while most problems iterate the launch is bound by HBM traffic and
+      // instruction issue at full occupancy; once most have returned, what is left is the dependent chain of the
+      // slowest problems. After `tail_at` iterations the unfinished problems are compacted (ordered) and finished by
+      // the tail instantiation: full warps again, one warp per block, no register cap. Same device functions, same
+      // per-problem arithmetic: results are bit-identical to the single launch.
+      int *d_counts, *d_nactive, cblocks;
+      compaction(d_counts, d_nactive, cblocks);
+      const int* fin = c.iscal + (size_t)I_FINISHED * c.Bp;
+      TPP_LAUNCH_BOX(tpp_solve_kernel, (nblocks(), TPP_BLOCK, 0, stream), c, maxiter, is_feasible, reginit, tail_at, 1, nullptr, nullptr, 0, c.B);
+      tpp_compact_count_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts);
+      tpp_compact_scatter_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts, d_list, d_nactive);
+      TPP_LAUNCH_BOX(tpp_solve_tail_kernel, ((c.B + 31) / 32, 32, 0, stream), c, maxiter, is_feasible, reginit, 0, 0, d_list, d_nactive, 0, c.B);
+      last_launches += 4;
+    } else {
+      TPP_LAUNCH_BOX(tpp_solve_kernel, (nblocks(), TPP_BLOCK, 0, stream), c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr, 0, c.B);
+      ++last_launches;
     }
     CGX_CUDA(cudaEventRecord(ev[2], stream));
     CGX_CUDA(cudaGetLastError());

@@ -211,6 +211,35 @@ def test_callbacks_replay_iterations():
 
 
 @pytest.mark.parametrize("kind", ["ddp", "fddp"])
+def test_two_phase_solve_with_tail_kernel_is_bit_identical(kind, monkeypatch):
+    """Large batches are solved in two launches: all problems for the first iterations, then the unfinished ones,
+    compacted, by the tail instantiation of the same loop (no register cap, one warp per block). Same device functions
+    and per-problem arithmetic: every result must be BIT-identical to the single launch, wherever the cut is."""
+    B, T = 4096 + 77, 25
+    x0, problem, solver, ob = _pair(kind, B, T, 123)
+    xs = np.repeat(x0[:, None, :], T + 1, 1)
+    us = np.zeros((B, T, 2))
+    monkeypatch.setenv("CROCODDYL_B200_TPP_TAIL_AT", "0")
+    solver.enableTrace(100)
+    conv0 = solver.solve(xs, us, 100, False, 1e-9)
+    ref = {f: solver.get(f) for f in ("xs", "us", "K", "k", "Vx", "Vxx", "fs")}
+    sc0 = solver.scalars()
+    tr0 = [solver.trace(b) for b in (0, 5, B - 1)]
+    assert sc0["n_records"].max() > 30, "the case must have problems that outlive the cut"
+    for cut in ("1", "7", "40"):
+        monkeypatch.setenv("CROCODDYL_B200_TPP_TAIL_AT", cut)
+        conv = solver.solve(xs, us, 100, False, 1e-9)
+        assert np.array_equal(conv, conv0), cut
+        sc = solver.scalars()
+        for k in sc0:
+            assert np.array_equal(sc[k], sc0[k]), (cut, k)
+        for f, v in ref.items():
+            assert np.array_equal(solver.get(f), v), (cut, f)
+        for b, t0 in zip((0, 5, B - 1), tr0):
+            assert np.array_equal(solver.trace(b), t0), (cut, b)
+
+
+@pytest.mark.parametrize("kind", ["ddp", "fddp"])
 def test_sliced_host_pipeline_equals_sequential_solve(kind, monkeypatch):
     """cgx_solver_solve_fetch on the thread-per-problem backend cuts the batch into slices on separate streams (copies of
     one slice overlap the solve of the others). Every slice runs the same kernel, so the results must be BIT-identical

@@ -18,7 +18,9 @@ struct SolverOpts {
 
 // per-problem scalar slots (double), stored as scal[slot * Bp + b]
 enum {
-  S_COST = 0, S_STOP, S_D0, S_D1, S_XREG, S_UREG, S_STEP, S_DV, S_DVEXP, S_COST_TRY, S_DG, S_DQ, S_DVGAP, S_NSLOTS
+  S_COST = 0, S_STOP, S_D0, S_D1, S_XREG, S_UREG, S_STEP, S_DV, S_DVEXP, S_COST_TRY, S_DG, S_DQ, S_DVGAP,
+  S_LBXREG, S_LBUREG, S_FLXREG /* thread-per-problem core: regularisation of the last successful / first failed backward pass */,
+  S_NSLOTS
 };
 // per-problem int slots, iscal[slot * Bp + b]
 enum {

@@ -34,10 +34,14 @@ struct TppCtx {
   int B, Bp, T;
   int fddp;       // 1 = SolverFDDP, 0 = SolverDDP
   int full;       // keep Qxx,Qxu,Quu,Qx,Qu per node
-  double* xu[2];  // [T+1][Bp][R_XU]
+  double* xu[2];  // [T+1][Bp][R_XU] candidate / trial: x, u, aux
+  double* fs;     // [T+1][Bp][R_FS] gaps of the candidate the last calcDiff ran on
+  double* w;      // [T+1][Bp][R_FS] w = Vxx fs of the last backward pass (infeasible candidates only)
   double* kk;     // [T][Bp][R_KK]
-  double* v;      // [T+1][Bp][R_V]
+  double* vx;     // [T+1][Bp][R_FS] Vx
+  double* vl;     // [T+1][Bp][R_VL] lower triangle of Vxx
   double* q;      // [T][Bp][R_Q] (full only)
+  int store_v;    // 1: every backward pass stores Vx / Vxx; 0: the solve loop materialises them once, at its end
   double* x0;     // [NX][Bp]
   double* scal;   // [S_NSLOTS][Bp]
   int* iscal;     // [I_NSLOTS][Bp]
@@ -54,18 +58,23 @@ struct TppCtx {
 };
 
 __host__ __device__ constexpr int rup4(int n) { return (n + 3) / 4 * 4; }
+__host__ __device__ constexpr int rup8(int n) { return (n + 7) / 8 * 8; }
 
 template <class M>
 struct TppLayout {
   static constexpr int N = M::NX, U = M::NU;
   static constexpr int NL = N * (N + 1) / 2;
-  // candidate / trial record: { x[N], u[U], aux[NA] | fs[N] } — the first group (whole sectors) is what a rollout
-  // writes and a backward pass reads; aux = per-node values calc leaves for calcDiff (unicycle: sin, cos of the heading,
-  // so that the backward pass needs no sincos of its own); the gaps have their own sector(s)
+  // Every record is a whole number of 64-byte DRAM atoms or a single 32-byte sector in an array of its own (adjacent
+  // lanes then complete each other's atoms): ncu of the 96-byte records of the first layouts showed 1.6x the algorithmic
+  // DRAM bytes (reads of 64 bytes straddling two atoms, partial-atom writes).
+  //   XU : { x[N], u[U], aux[NA] }  candidate / trial; aux = per-node values calc leaves for calcDiff (unicycle: sin,
+  //        cos of the heading, so that the backward pass needs no sincos of its own)
+  //   FS : { fs[N] }   W : { w[N] = Vxx fs }   VX : { Vx[N] }   VL : { lower triangle of Vxx, column-major }
+  //   KK : { K[U*N] column-major, k[U] }
   static constexpr int NA = M::NAUX;
-  static constexpr int XU_X = 0, XU_U = N, XU_A = N + U, XU_F = rup4(N + U + NA), R_XU = XU_F + rup4(N);
-  static constexpr int KK_K = 0, KK_k = U * N, R_KK = rup4(U * N + U);
-  static constexpr int V_W = 0, V_VX = N, V_VXX = 2 * N, R_V = rup4(2 * N + NL);
+  static constexpr int XU_X = 0, XU_U = N, XU_A = N + U, R_XU = rup8(N + U + NA);
+  static constexpr int R_FS = rup4(N), R_VL = rup8(NL);
+  static constexpr int KK_K = 0, KK_k = U * N, R_KK = rup8(U * N + U);
   static constexpr int Q_XX = 0, Q_XU = N * N, Q_UU = Q_XU + N * U, Q_X = Q_UU + U * U, Q_U = Q_X + N,
                        R_Q = rup4(Q_U + U);
   // index of (i,j), i >= j, in the column-major packed lower triangle
@@ -241,7 +250,7 @@ struct UnicycleModel {
 template <class M>
 TPP_SWEEP_ATTR double tpp_calc_pass(const TppCtx& c, const M& m, int b, double* __restrict__ xu) {
   typedef TppLayout<M> L;
-  constexpr int N = M::NX, U = M::NU, SXA = L::XU_F / 4, SA0 = L::XU_A / 4;
+  constexpr int N = M::NX, U = M::NU, SXA = L::R_XU / 4, SA0 = L::XU_A / 4;
   const int Bp = c.Bp, T = c.T;
   const size_t stride = (size_t)Bp * L::R_XU;
   double* p = xu + (size_t)b * L::R_XU;
@@ -289,52 +298,58 @@ TPP_SWEEP_ATTR double tpp_calc_pass(const TppCtx& c, const M& m, int b, double* 
     }                                            \
   } while (0)
 
-// fszero: bit i set = the gap sectors of candidate buffer i hold zeros (kept across the iterations of one solve so
-// that a feasible candidate zero-fills them once per buffer, ddp.cpp:172-176)
-// GAPS = !is_feasible: the feasible instantiation carries no gap / w arithmetic and no record of node t + 1 at all
-// (most sweeps of a solve run on a feasible candidate)
-template <class M, bool BOX, bool GAPS>
+// fszero: bit 0 set = the gap array holds zeros (kept across the iterations of one solve so that a feasible candidate
+// zero-fills it once, ddp.cpp:172-176).
+// GAPS = !is_feasible: the feasible instantiation carries no gap / w arithmetic and no data of node t + 1 at all
+// (most sweeps of a solve run on a feasible candidate).
+// STORE: 0 = gains only (K, k; Vx / Vxx stay in registers: the solve loop materialises them once, after its last
+// backward pass), 1 = everything (step-wise API, full storage), 2 = Vx / Vxx only (the materialising pass: recomputes
+// the last backward pass on the same candidate, gaps and regularisation and stores nothing else).
+template <class M, bool BOX, bool GAPS, int STORE>
 TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, TppStage& stg, int b, int cur, bool recalc, double xreg,
                                      double ureg, double& dg_out, double& dq_out, double& stop_out, int& fszero) {
   constexpr bool is_feasible = !GAPS;
+  constexpr bool ST_V = STORE != 0, ST_K = STORE != 2;
   typedef TppLayout<M> L;
   constexpr int N = M::NX, U = M::NU, NL = L::NL;
-  constexpr int SR = L::R_XU / 4, SXA = L::XU_F / 4;
+  constexpr int SXA = L::R_XU / 4, SFS = L::R_FS / 4;
   const int Bp = c.Bp, T = c.T;
   const bool fddp = c.fddp != 0;
-  const bool full = c.full != 0;
-  const size_t sxu = (size_t)Bp * L::R_XU, skk = (size_t)Bp * L::R_KK, sv = (size_t)Bp * L::R_V;
-  double* pxu = c.xu[cur] + ((size_t)T * Bp + b) * L::R_XU;   // record of node t + 1 while node t is visited
-  double* pv = c.v + ((size_t)T * Bp + b) * L::R_V;
-  double* pkk = c.kk + ((size_t)(T - 1) * Bp + b) * L::R_KK;  // record of node t
+  const bool full = c.full != 0 && ST_K;
+  const size_t sxu = (size_t)Bp * L::R_XU, skk = (size_t)Bp * L::R_KK, sfs = (size_t)Bp * L::R_FS, svl = (size_t)Bp * L::R_VL;
+  const double* pxu = c.xu[cur] + ((size_t)T * Bp + b) * L::R_XU;  // record of node t + 1 while node t is visited
+  double* pfs = c.fs + ((size_t)T * Bp + b) * L::R_FS;             // gaps / w / Vx of node t + 1
+  double* pw = c.w + ((size_t)T * Bp + b) * L::R_FS;
+  double* pvx = c.vx + ((size_t)T * Bp + b) * L::R_FS;
+  double* pvl = c.vl + ((size_t)T * Bp + b) * L::R_VL;
+  double* pkk = c.kk + ((size_t)(T - 1) * Bp + b) * L::R_KK;       // record of node t
   double dg = 0., dq = 0., stop = 0.;
   const bool has_xreg = !isnan(xreg), has_ureg = !isnan(ureg);  // ddp.cpp:185,216,226,237
   // gaps: read back when they are not recomputed (only an infeasible candidate uses them)
   const bool load_fs = GAPS && !recalc;
-  const bool zero_fs = !GAPS && recalc && !((fszero >> cur) & 1);
+  const bool zero_fs = !GAPS && recalc && !(fszero & 1);
   double Vl[NL], Vx[N];
   double Fx[N * N], Fu[N * U], Lx[N], Lu[U], Lxx[N * N], Lxu[N * U], Luu[U * U], xn[N];
-  // records: rp = node t + 1 (x and the gaps: GAPS only) and r = node t in registers; node t - 1 is on its way into
-  // the shared-memory staging buffer while node t is computed
-  constexpr int RW = GAPS ? L::R_XU : L::XU_F;  // the feasible instantiation never holds a gap sector
-  constexpr int CF = 2 * SXA;                    // staging chunk of the gap sector(s)
-  static_assert(2 * SR <= TPP_STG_CHUNKS, "staging area too small for this model");
-  double rp[L::R_XU], r[RW];
+  // node t's record comes out of the shared-memory staging buffer; node t - 1 is on its way into the other buffer while
+  // node t is computed. GAPS only: xp / fp = x and gaps of node t + 1, fr = gaps of node t (read back when not recomputed)
+  constexpr int CF = 2 * SXA;  // staging chunks of the gap record
+  static_assert(2 * (SXA + SFS) <= TPP_STG_CHUNKS, "staging area too small for this model");
+  double r[L::R_XU], xp[N], fp[L::R_FS], fr[L::R_FS];
 #pragma unroll
-  for (int i = 0; i < L::R_XU; ++i) rp[i] = 0.;
-#pragma unroll
-  for (int i = 0; i < RW; ++i) r[i] = 0.;
+  for (int i = 0; i < L::R_FS; ++i) fp[i] = fr[i] = 0.;
   int buf = 0;
   stg_wait();  // nothing of an earlier sweep (one that returned on an error) may still be landing in the staging area
   // node T - 1 into the staging buffer, then the terminal node (ddp.cpp:181-187): u = unone_ = 0 (action-base.hxx:27-37)
   stg_issue<0, SXA>(stg, buf, pxu - sxu);
   if constexpr (GAPS) {
-    if (load_fs) stg_issue<CF, SR - SXA>(stg, buf, pxu - sxu + L::XU_F);
+    if (load_fs) stg_issue<CF, SFS>(stg, buf, pfs - sfs);
   }
   stg_commit();
-  ld_rec<0, SXA>(pxu, rp);
+  ld_rec<0, SXA>(pxu, r);
   if constexpr (GAPS) {
-    if (load_fs) ld_rec<SXA, SR>(pxu, rp);
+    if (load_fs) ld_rec<0, SFS>(pfs, fp);
+#pragma unroll
+    for (int i = 0; i < N; ++i) xp[i] = r[L::XU_X + i];
   }
   {
     double u0[U];
@@ -342,7 +357,7 @@ TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, TppStage& stg,
     for (int i = 0; i < U; ++i) u0[i] = 0.;
     M mt;
     mt.load(c.tparams);
-    mt.calcBothAux(rp + L::XU_X, u0, rp + L::XU_A, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);  // only Lx, Lxx are used
+    mt.calcBothAux(r + L::XU_X, u0, r + L::XU_A, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);  // only Lx, Lxx are used
   }
 #pragma unroll
   for (int j = 0; j < N; ++j)
@@ -356,7 +371,7 @@ TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, TppStage& stg,
       stg_wait();
       stg_read<0, SXA>(stg, buf, r);
       if constexpr (GAPS) {
-        if (load_fs) stg_read<CF, SR - SXA>(stg, buf, r + L::XU_F);
+        if (load_fs) stg_read<CF, SFS>(stg, buf, fr);
       }
       buf ^= 1;
       // node t-1's record is requested (cp.async into the other staging buffer) before node t's dependent Riccati
@@ -364,14 +379,14 @@ TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, TppStage& stg,
       if (t > 0) {
         stg_issue<0, SXA>(stg, buf, pxu - 2 * sxu);
         if constexpr (GAPS) {
-          if (load_fs) stg_issue<CF, SR - SXA>(stg, buf, pxu - 2 * sxu + L::XU_F);
+          if (load_fs) stg_issue<CF, SFS>(stg, buf, pfs - 2 * sfs);
         }
         stg_commit();
       }
       if (t > TPP_PF_DIST) {
         pf_rec<0, SXA>(pxu - (2 + TPP_PF_DIST) * sxu);
         if constexpr (GAPS) {
-          if (load_fs) pf_rec<SXA, SR>(pxu - (2 + TPP_PF_DIST) * sxu);
+          if (load_fs) pf_rec<0, SFS>(pfs - (2 + TPP_PF_DIST) * sfs);
         }
       }
       m.calcBothAux(r + L::XU_X, r + L::XU_U, r + L::XU_A, xn, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu);
@@ -380,53 +395,54 @@ TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, TppStage& stg,
 #pragma unroll
       for (int i = 0; i < N; ++i) xn[i] = c.x0[(size_t)i * Bp + b];
     }
-    // ---- finish node t+1: gap term, V record ----
-    double vrec[L::R_V];
-#pragma unroll
-    for (int i = 0; i < L::R_V; ++i) vrec[i] = 0.;
+    // ---- finish node t+1: gap term, w, Vx / Vxx records ----
     if constexpr (GAPS) {
       if (recalc) {
 #pragma unroll
-        for (int i = 0; i < N; ++i) rp[L::XU_F + i] = xn[i] - rp[L::XU_X + i];
-#pragma unroll
-        for (int i = L::XU_F + N; i < L::R_XU; ++i) rp[i] = 0.;
-        st_rec<SXA, SR>(pxu, rp);
+        for (int i = 0; i < N; ++i) fp[i] = xn[i] - xp[i];
+        if (ST_K) st_rec<0, SFS>(pfs, fp);
       }
-      const double* f = rp + L::XU_F;
+      double wv[L::R_FS];
+#pragma unroll
+      for (int i = 0; i < L::R_FS; ++i) wv[i] = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) {
         double s = 0.;
 #pragma unroll
-        for (int j = 0; j < N; ++j) s += Vl[L::sym(i, j)] * f[j];
-        vrec[L::V_W + i] = s;
+        for (int j = 0; j < N; ++j) s += Vl[L::sym(i, j)] * fp[j];
+        wv[i] = s;
         Vx[i] += s;
       }
+      if (ST_K) st_rec<0, SFS>(pw, wv);
       if (fddp) {  // updateExpectedImprovement gap terms (fddp.cpp:131-135,141-145)
         double a = 0., q = 0.;
 #pragma unroll
         for (int i = 0; i < N; ++i) {
-          a += Vx[i] * f[i];
-          q += f[i] * vrec[L::V_W + i];
+          a += Vx[i] * fp[i];
+          q += fp[i] * wv[i];
         }
         dg -= a;
         dq += q;
       }
     } else if (zero_fs) {
-#pragma unroll
-      for (int i = L::XU_F; i < L::R_XU; ++i) rp[i] = 0.;  // ddp.cpp:172-176
-      st_rec<SXA, SR>(pxu, rp);
+      st_rec<0, SFS>(pfs, fp);  // zeros: ddp.cpp:172-176
     }
     {
       double nrm = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) {
-        vrec[L::V_VX + i] = Vx[i];
         const double v = fabs(Vx[i]);
         if (!(v <= nrm)) nrm = v;
       }
+      if (ST_V) {
+        double vrec[L::R_FS], lrec[L::R_VL];
 #pragma unroll
-      for (int i = 0; i < NL; ++i) vrec[L::V_VXX + i] = Vl[i];
-      st_rec<0, L::R_V / 4>(pv, vrec);
+        for (int i = 0; i < L::R_FS; ++i) vrec[i] = i < N ? Vx[i] : 0.;
+#pragma unroll
+        for (int i = 0; i < L::R_VL; ++i) lrec[i] = i < NL ? Vl[i] : 0.;
+        st_rec<0, SFS>(pvx, vrec);
+        st_rec<0, L::R_VL / 4>(pvl, lrec);
+      }
       if (t + 1 < T && raise_if_nan(nrm)) return 1;  // ddp.cpp:246-248
     }
     if (t < 0) break;
@@ -609,7 +625,7 @@ TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, TppStage& stg,
       dq -= q;
       stop += st;
     }
-    st_rec<0, L::R_KK / 4>(pkk, kkrec);
+    if (ST_K) st_rec<0, L::R_KK / 4>(pkk, kkrec);
     if (full) {
       double qrec[L::R_Q];
 #pragma unroll
@@ -668,30 +684,35 @@ TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, TppStage& stg,
     if (raise_if_nan(nrm)) return 1;  // ddp.cpp:249-251
     if constexpr (GAPS) {
 #pragma unroll
-      for (int i = 0; i < L::R_XU; ++i) rp[i] = r[i];
+      for (int i = 0; i < N; ++i) xp[i] = r[L::XU_X + i];
+      if (load_fs) {
+#pragma unroll
+        for (int i = 0; i < L::R_FS; ++i) fp[i] = fr[i];
+      }
     }
     pxu -= sxu;
-    pv -= sv;
+    pfs -= sfs;
+    pw -= sfs;
+    pvx -= sfs;
+    pvl -= svl;
     pkk -= skk;
   }
-  if (recalc) {  // what the gap sectors of this buffer hold now
-    if (is_feasible)
-      fszero |= 1 << cur;
-    else
-      fszero &= ~(1 << cur);
-  }
+  if (recalc && ST_K) fszero = is_feasible ? 1 : 0;  // what the gap array holds now
   dg_out = dg;
   dq_out = dq;
   stop_out = stop;
   return 0;
 }
+// store: 0 = gains only, 1 = everything, 2 = Vx / Vxx only (see tpp_backward_impl)
 template <class M, bool BOX = false>
 TPP_SWEEP_ATTR int tpp_backward(const TppCtx& c, const M& m, TppStage& stg, int b, int cur, bool recalc, bool is_feasible,
-                                bool was_feasible, double xreg, double ureg, double& dg_out, double& dq_out,
-                                double& stop_out, int& fszero) {
-  (void)was_feasible;
-  if (is_feasible) return tpp_backward_impl<M, BOX, false>(c, m, stg, b, cur, recalc, xreg, ureg, dg_out, dq_out, stop_out, fszero);
-  return tpp_backward_impl<M, BOX, true>(c, m, stg, b, cur, recalc, xreg, ureg, dg_out, dq_out, stop_out, fszero);
+                                int store, double xreg, double ureg, double& dg_out, double& dq_out, double& stop_out,
+                                int& fszero) {
+#define TPP_BWD(G, S) tpp_backward_impl<M, BOX, G, S>(c, m, stg, b, cur, recalc, xreg, ureg, dg_out, dq_out, stop_out, fszero)
+  if (store == 0) return is_feasible ? TPP_BWD(false, 0) : TPP_BWD(true, 0);
+  if (store == 2) return is_feasible ? TPP_BWD(false, 2) : TPP_BWD(true, 2);
+  return is_feasible ? TPP_BWD(false, 1) : TPP_BWD(true, 1);
+#undef TPP_BWD
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -706,7 +727,7 @@ TPP_SWEEP_ATTR int tpp_forward_impl(const TppCtx& c, const M& m, TppStage& stg, 
                                     bool is_feasible, double& cost_try_out, double& dv_out) {
   typedef TppLayout<M> L;
   constexpr int N = M::NX, U = M::NU;
-  constexpr int SR = L::R_XU / 4, SK = L::R_KK / 4, SW = rup4(N) / 4;
+  constexpr int SXA = L::R_XU / 4, SK = L::R_KK / 4, SFS = L::R_FS / 4;
   const int Bp = c.Bp, T = c.T;
   const bool fddp = c.fddp != 0;
   const bool closed = !GAPS || !fddp || is_feasible || (alpha == 1.);
@@ -724,27 +745,26 @@ TPP_SWEEP_ATTR int tpp_forward_impl(const TppCtx& c, const M& m, TppStage& stg, 
       uub[i] = c.u_ub[(size_t)b * U + i];
     }
   }
-  constexpr int SXA = L::XU_F / 4;
   const bool need_fs = !closed || term_open;  // the gaps are read only by an open rollout
-  const size_t sxu = (size_t)Bp * L::R_XU, skk = (size_t)Bp * L::R_KK, sv = (size_t)Bp * L::R_V;
+  const size_t sxu = (size_t)Bp * L::R_XU, skk = (size_t)Bp * L::R_KK, sfs = (size_t)Bp * L::R_FS;
   const double* __restrict__ pxu = c.xu[cur] + (size_t)b * L::R_XU;  // candidate record of node t + 1 (prefetched)
   double* __restrict__ pxt = c.xu[cur ^ 1] + (size_t)b * L::R_XU;    // trial record of node t
   const double* __restrict__ pkk = c.kk + (size_t)b * L::R_KK;
-  const double* __restrict__ pv = c.v + (size_t)b * L::R_V;
+  const double* __restrict__ pfs = c.fs + (size_t)b * L::R_FS;
+  const double* __restrict__ pw = c.w + (size_t)b * L::R_FS;
   double cost_try = 0., dv = 0.;
   double xn[N], xt[N], dx[N];
   // node t+1's inputs (none of them depends on the rollout recursion) travel into the shared-memory staging buffer
   // while node t is computed: chunks [0, CK) = x,u,aux  [CK, CFS) = K,k  then the gaps and w (GAPS only)
-  constexpr int RW = GAPS ? L::R_XU : L::XU_F;
-  constexpr int CK = 2 * SXA, CFS = CK + 2 * SK, CW = CFS + 2 * (SR - SXA);
-  static_assert(CW + 2 * SW <= TPP_STG_CHUNKS, "staging area too small for this model");
+  constexpr int CK = 2 * SXA, CFS = CK + 2 * SK, CW = CFS + 2 * SFS;
+  static_assert(CW + 2 * SFS <= TPP_STG_CHUNKS, "staging area too small for this model");
   int buf = 0;
   stg_wait();  // nothing of an earlier sweep may still be landing in the staging area
   auto fetch = [&](int t) {  // node t's inputs; the pointers stand on node t
     stg_issue<0, SXA>(stg, buf, pxu);
     if constexpr (GAPS) {
-      if (need_fs) stg_issue<CFS, SR - SXA>(stg, buf, pxu + L::XU_F);
-      if (use_w) stg_issue<CW, SW>(stg, buf, pv);
+      if (need_fs) stg_issue<CFS, SFS>(stg, buf, pfs);
+      if (use_w) stg_issue<CW, SFS>(stg, buf, pw);
     }
     if (t < T) stg_issue<CK, SK>(stg, buf, pkk);
     stg_commit();
@@ -753,33 +773,27 @@ TPP_SWEEP_ATTR int tpp_forward_impl(const TppCtx& c, const M& m, TppStage& stg, 
   for (int i = 0; i < N; ++i) xn[i] = c.x0[(size_t)i * Bp + b];
   fetch(0);
   for (int t = 0; t <= T; ++t) {
-    double ca[RW], ck[L::R_KK], cw[N], o[4 * SXA];
+    double ca[L::R_XU], ck[L::R_KK], cf[L::R_FS], cw[L::R_FS], o[L::R_XU];
 #pragma unroll
-    for (int i = 0; i < RW; ++i) ca[i] = 0.;
-#pragma unroll
-    for (int i = 0; i < N; ++i) cw[i] = 0.;
+    for (int i = 0; i < L::R_FS; ++i) cf[i] = cw[i] = 0.;
     stg_wait();
     stg_read<0, SXA>(stg, buf, ca);
     if (t < T) stg_read<CK, SK>(stg, buf, ck);
     if constexpr (GAPS) {
-      if (need_fs) stg_read<CFS, SR - SXA>(stg, buf, ca + L::XU_F);
-      if (use_w) {
-        double w4[4 * SW];
-        stg_read<CW, SW>(stg, buf, w4);
-#pragma unroll
-        for (int i = 0; i < N; ++i) cw[i] = w4[L::V_W + i];
-      }
+      if (need_fs) stg_read<CFS, SFS>(stg, buf, cf);
+      if (use_w) stg_read<CW, SFS>(stg, buf, cw);
     }
     buf ^= 1;
     pxu += sxu;
     pkk += skk;
-    pv += sv;
+    pfs += sfs;
+    pw += sfs;
     if (t < T) fetch(t + 1);
     if (t + TPP_PF_DIST <= T) {  // node t + TPP_PF_DIST into L2
       pf_rec<0, SXA>(pxu + (TPP_PF_DIST - 1) * sxu);
       if constexpr (GAPS) {
-        if (need_fs) pf_rec<SXA, SR>(pxu + (TPP_PF_DIST - 1) * sxu);
-        if (use_w) pf_rec<0, SW>(pv + (TPP_PF_DIST - 1) * sv);
+        if (need_fs) pf_rec<0, SFS>(pfs + (TPP_PF_DIST - 1) * sfs);
+        if (use_w) pf_rec<0, SFS>(pw + (TPP_PF_DIST - 1) * sfs);
       }
       if (t + TPP_PF_DIST < T) pf_rec<0, SK>(pkk + (TPP_PF_DIST - 1) * skk);
     }
@@ -788,7 +802,7 @@ TPP_SWEEP_ATTR int tpp_forward_impl(const TppCtx& c, const M& m, TppStage& stg, 
       for (int i = 0; i < N; ++i) xt[i] = xn[i];
     } else if constexpr (GAPS) {
 #pragma unroll
-      for (int i = 0; i < N; ++i) xt[i] = xn[i] + ca[L::XU_F + i] * am1;  // integrate(xnext, fs*(a-1))
+      for (int i = 0; i < N; ++i) xt[i] = xn[i] + cf[i] * am1;  // integrate(xnext, fs*(a-1))
     }
 #pragma unroll
     for (int i = 0; i < 4 * SXA; ++i) o[i] = 0.;
@@ -890,8 +904,15 @@ __device__ __forceinline__ void tpp_solve_body(const TppCtx& c, TppStage& stg, i
   double steplength = TPP_S(S_STEP), dV = TPP_S(S_DV), dVexp = TPP_S(S_DVEXP), cost_try = TPP_S(S_COST_TRY);
   double dg = 0., dq = 0.;
   int nbwd = 0, nfwd = 0, nrec = 0, converged = 0, iter = 0;
-  int fszero = 0;  // what the gap sectors of the two candidate buffers hold (tpp_backward)
+  int fszero = 0;  // does the gap array hold zeros (tpp_backward)
   bool recalc = true, need_gaps = true, done = false;
+  // Vx / Vxx are not stored by the backward passes of the loop (store == 0): they are materialised once, when solve()
+  // returns, by repeating the last successful backward pass (lb_*) — and the failed attempts after it, if the loop ended
+  // on them (fl_*: the reference's arrays hold their partial overwrites) — with stores of Vx / Vxx only
+  const int store = c.store_v ? 1 : 0;
+  bool has_lb = false, lb_feas = false;
+  int lb_cur = 0, nfail = 0;
+  double lb_xreg = 0., lb_ureg = 0., fl_xreg = 0.;
   if (!first) {  // resume
     feas = TPP_I(I_FEAS) != 0;
     wasfeas = TPP_I(I_WASFEAS) != 0;
@@ -906,7 +927,14 @@ __device__ __forceinline__ void tpp_solve_body(const TppCtx& c, TppStage& stg, i
     const int lp = TPP_I(I_LOOP);
     recalc = (lp & 1) != 0;
     need_gaps = (lp & 2) != 0;
-    fszero = (lp >> 2) & 3;
+    fszero = (lp >> 2) & 1;
+    has_lb = (lp >> 3) & 1;
+    lb_cur = (lp >> 4) & 1;
+    lb_feas = (lp >> 5) & 1;
+    nfail = lp >> 8;
+    lb_xreg = TPP_S(S_LBXREG);
+    lb_ureg = TPP_S(S_LBUREG);
+    fl_xreg = TPP_S(S_FLXREG);
   }
   int budget = chunk > 0 ? chunk : maxiter + 1;
   bool paused = false;
@@ -923,12 +951,19 @@ __device__ __forceinline__ void tpp_solve_body(const TppCtx& c, TppStage& stg, i
     if (recalc) need_gaps = true;
     while (true) {  // computeDirection with regularisation retry (ddp.cpp:55-68)
       if (need_gaps) fsbuf = cur;
-      const int st = tpp_backward<M, BOX>(c, m, stg, b, cur, need_gaps, feas, wasfeas, xreg, ureg, dg, dq, stop, fszero);
+      const int st = tpp_backward<M, BOX>(c, m, stg, b, cur, need_gaps, feas, store, xreg, ureg, dg, dq, stop, fszero);
       ++nbwd;
       if (st == 0) {
         need_gaps = false;
+        has_lb = true;
+        lb_cur = cur;
+        lb_feas = feas;
+        lb_xreg = xreg;
+        lb_ureg = ureg;
+        nfail = 0;
         break;
       }
+      if (nfail++ == 0) fl_xreg = xreg;
       recalc = false;
       reg_increase(c.o, xreg, ureg);
       ++retries;
@@ -993,6 +1028,19 @@ __device__ __forceinline__ void tpp_solve_body(const TppCtx& c, TppStage& stg, i
       break;  // return true with iter_ = iter
     }
   }
+  if (!paused && store == 0) {  // solve() has returned: materialise Vx / Vxx (see above)
+    double g0, g1, g2;
+    int fz = 0;
+    if (has_lb) tpp_backward<M, BOX>(c, m, stg, b, lb_cur, false, lb_feas, 2, lb_xreg, lb_ureg, g0, g1, g2, fz);
+    double fx = fl_xreg, fu = fl_xreg;
+    for (int i = 0; i < nfail; ++i) {  // the failed attempts the loop ended on, in their order
+      tpp_backward<M, BOX>(c, m, stg, b, cur, true, feas, 2, fx, fu, g0, g1, g2, fz);
+      reg_increase(c.o, fx, fu);
+    }
+  }
+  TPP_S(S_LBXREG) = lb_xreg;
+  TPP_S(S_LBUREG) = lb_ureg;
+  TPP_S(S_FLXREG) = fl_xreg;
   TPP_S(S_COST) = cost;
   TPP_S(S_STOP) = stop;
   TPP_S(S_D0) = d0;
@@ -1014,7 +1062,8 @@ __device__ __forceinline__ void tpp_solve_body(const TppCtx& c, TppStage& stg, i
   TPP_I(I_NREC) = nrec;
   TPP_I(I_NBWD) = nbwd;
   TPP_I(I_NFWD) = nfwd;
-  TPP_I(I_LOOP) = (recalc ? 1 : 0) | (need_gaps ? 2 : 0) | (fszero << 2);
+  TPP_I(I_LOOP) = (recalc ? 1 : 0) | (need_gaps ? 2 : 0) | ((fszero & 1) << 2) | ((has_lb ? 1 : 0) << 3) | (lb_cur << 4) |
+                  ((lb_feas ? 1 : 0) << 5) | (nfail << 8);
   TPP_I(I_FINISHED) = paused ? 0 : 1;
 }
 // The whole batch in ONE wave: 8 blocks of 64 threads per SM = 128 registers per thread (measured: with 144 registers
@@ -1093,8 +1142,9 @@ __global__ void __launch_bounds__(64) tpp_direction_kernel(const __grid_constant
     TPP_I(I_FSBUF) = cur;
   }
   double dg = 0., dq = 0., stop = 0.;
-  int fszero = 0;  // step-wise call: a feasible candidate always zero-fills its gap sectors
-  const int st = tpp_backward<M, BOX>(c, m, stg, b, cur, recalc != 0, feas, wasfeas, TPP_S(S_XREG), TPP_S(S_UREG), dg, dq, stop,
+  int fszero = 0;  // step-wise call: a feasible candidate always zero-fills the gap array
+  (void)wasfeas;
+  const int st = tpp_backward<M, BOX>(c, m, stg, b, cur, recalc != 0, feas, 1, TPP_S(S_XREG), TPP_S(S_UREG), dg, dq, stop,
                                       fszero);
   TPP_I(I_BSTATUS) = st;
   if (st == 0) {

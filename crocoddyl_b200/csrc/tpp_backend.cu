@@ -104,7 +104,10 @@ struct TppBackend : Backend {
     if (!solver_allocated) {
       for (int i = 0; i < 2; ++i) c.xu[i] = alloc((T + 1) * Bp * L::R_XU);
       c.kk = alloc(T * Bp * L::R_KK);
-      c.v = alloc((T + 1) * Bp * L::R_V);
+      c.fs = alloc((T + 1) * Bp * L::R_FS);
+      c.w = alloc((T + 1) * Bp * L::R_FS);
+      c.vx = alloc((T + 1) * Bp * L::R_FS);
+      c.vl = alloc((T + 1) * Bp * L::R_VL);
       c.scal = alloc((size_t)S_NSLOTS * Bp);
       int* is = dalloc<int>((size_t)I_NSLOTS * Bp);
       allocs.push_back(is);
@@ -124,6 +127,9 @@ struct TppBackend : Backend {
     if (full && !c.q) c.q = alloc(T * Bp * L::R_Q);
     if (c.box && !c.quu_inv) c.quu_inv = alloc(T * Bp * U * U);
     c.full = full;
+    // lean storage: Vx / Vxx are materialised once per solve (tpp.cuh); full storage and the box solvers (whose QP is
+    // warm-started from the previous gains) store them in every backward pass
+    c.store_v = (full || c.box) ? 1 : 0;
     if (trace_on && (!c.trace || c.trace_cap != trace_cap)) {
       release(c.trace);
       c.trace = alloc((size_t)trace_cap * NTRACE * Bp);
@@ -153,7 +159,7 @@ struct TppBackend : Backend {
   // (0 = never). CROCODDYL_B200_TPP_TAIL_AT overrides (development knob).
   int tail_iter() const {
     const char* e = getenv("CROCODDYL_B200_TPP_TAIL_AT");
-    return e ? atoi(e) : 40;
+    return e ? atoi(e) : 22;
   }
   int chunk_iters() const {
     const char* e = getenv("CROCODDYL_B200_TPP_CHUNK");
@@ -340,14 +346,18 @@ struct TppBackend : Backend {
       if (size > 16) throw Unsupported("field too wide for the thread-per-problem backend");
       for (int i = 0; i < size; ++i) f.fm.off[i] = off0 + i;
     };
-    if (n == "xs" || n == "xs_try" || n == "us" || n == "us_try" || n == "fs") {
+    if (n == "xs" || n == "xs_try" || n == "us" || n == "us_try") {
       f.a = c.xu[0];
       f.b = c.xu[1];
-      f.sel = (n == "fs") ? fs_sel() : cur_sel();
+      f.sel = cur_sel();
       f.flip = (n == "xs_try" || n == "us_try") ? 1 : 0;
       if (n[0] == 'x') seq(L::R_XU, N, T + 1, L::XU_X);
-      else if (n[0] == 'u') seq(L::R_XU, U, T, L::XU_U);
-      else seq(L::R_XU, N, T + 1, L::XU_F);
+      else seq(L::R_XU, U, T, L::XU_U);
+      return f;
+    }
+    if (n == "fs") {
+      f.a = f.b = c.fs;
+      seq(L::R_FS, N, T + 1, 0);
       return f;
     }
     if (n == "K" || n == "k") {
@@ -362,15 +372,16 @@ struct TppBackend : Backend {
       seq(U * U, U * U, T, 0);
       return f;
     }
-    if (n == "Vx" || n == "Vxx") {
-      f.a = f.b = c.v;
-      if (n == "Vx") {
-        seq(L::R_V, N, T + 1, L::V_VX);
-      } else {
-        seq(L::R_V, N * N, T + 1, 0);
-        for (int j = 0; j < N; ++j)
-          for (int i = 0; i < N; ++i) f.fm.off[i + N * j] = L::V_VXX + L::sym(i, j);
-      }
+    if (n == "Vx") {
+      f.a = f.b = c.vx;
+      seq(L::R_FS, N, T + 1, 0);
+      return f;
+    }
+    if (n == "Vxx") {
+      f.a = f.b = c.vl;
+      seq(L::R_VL, N * N, T + 1, 0);
+      for (int j = 0; j < N; ++j)
+        for (int i = 0; i < N; ++i) f.fm.off[i + N * j] = L::sym(i, j);
       return f;
     }
     if (n == "Qxx" || n == "Qxu" || n == "Quu" || n == "Qx" || n == "Qu") {

@@ -1096,9 +1096,10 @@ __global__ void __launch_bounds__(1024) tpp_compact_count_kernel(const int* __re
   if (threadIdx.x == 0) counts[blockIdx.x] = n;
 }
 __global__ void __launch_bounds__(1024) tpp_compact_scatter_kernel(const int* __restrict__ finished, int B,
-                                                                   const int* __restrict__ counts, int* list, int* nactive) {
+                                                                   const int* __restrict__ counts, int* list, int* nactive,
+                                                                   int base) {
   __shared__ int warp_off[32];
-  __shared__ int base;
+  __shared__ int base_off;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int b = blockIdx.x * 1024 + tid;
   const int act = (b < B && finished[b] == 0) ? 1 : 0;
@@ -1107,7 +1108,7 @@ __global__ void __launch_bounds__(1024) tpp_compact_scatter_kernel(const int* __
   if (tid == 0) {
     int s = 0;
     for (int i = 0; i < (int)blockIdx.x; ++i) s += counts[i];
-    base = s;
+    base_off = s;
     if (blockIdx.x == gridDim.x - 1) *nactive = s + counts[blockIdx.x];
   }
   __syncthreads();
@@ -1120,7 +1121,7 @@ __global__ void __launch_bounds__(1024) tpp_compact_scatter_kernel(const int* __
     warp_off[lane] = x - v;
   }
   __syncthreads();
-  if (act) list[base + warp_off[wid] + __popc(bal & ((1u << lane) - 1u))] = b;
+  if (act) list[base_off + warp_off[wid] + __popc(bal & ((1u << lane) - 1u))] = base + b;  // base: first problem of the slice
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -161,6 +161,12 @@ struct TppBackend : Backend {
     const char* e = getenv("CROCODDYL_B200_TPP_TAIL_AT");
     return e ? atoi(e) : 22;
   }
+  // compaction scratch: [Bp] problem indices, per-1024-block counts (room for PIPE_MAX ragged slices), counters
+  void ensure_list() {
+    if (d_list) return;
+    d_list = dalloc<int>((size_t)c.Bp + (c.B + 1023) / 1024 + 2 * PIPE_MAX + 2);
+    allocs.push_back(d_list);
+  }
   int chunk_iters() const {
     const char* e = getenv("CROCODDYL_B200_TPP_CHUNK");
     return e ? atoi(e) : 0;
@@ -208,6 +214,10 @@ struct TppBackend : Backend {
     CGX_CUDA(cudaEventRecord(ev[1], stream));
     const int per = ((c.B + K - 1) / K + 63) / 64 * 64;
     const Fld fx = fld("xs"), fu = fld("us");
+    const int tail_at = tail_iter();
+    const bool two_phase = tail_at > 0 && maxiter > tail_at && c.B >= 4096;
+    if (two_phase) ensure_list();
+    int cb0 = 0;
     for (int k = 0; k < K; ++k) {
       const int b0 = k * per;
       if (b0 >= c.B) break;
@@ -221,9 +231,24 @@ struct TppBackend : Backend {
       gather(d_xs + ox, fx.fm, c.xu[0], c.xu[0], nullptr, 0, b0, nb, 1, st);
       gather(d_us + ou, fu.fm, c.xu[0], c.xu[0], nullptr, 0, b0, nb, 1, st);
       if (ptrace) CGX_CUDA(cudaEventRecord(ptime[k][0], st));
-      TPP_LAUNCH_BOX(tpp_solve_kernel, ((nb + 63) / 64, TPP_BLOCK, 0, st), c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr,
-                                                               b0, b0 + nb);
-      ++last_launches;
+      if (two_phase) {  // as solve(): the slice's unfinished problems are compacted and finished by the tail kernel
+        const int cb = (nb + 1023) / 1024;
+        int* cnt = d_list + c.Bp + cb0;
+        int* nact = d_list + c.Bp + (c.B + 1023) / 1024 + PIPE_MAX + 1 + k;
+        cb0 += cb;
+        const int* fin = c.iscal + (size_t)I_FINISHED * c.Bp + b0;
+        TPP_LAUNCH_BOX(tpp_solve_kernel, ((nb + 63) / 64, TPP_BLOCK, 0, st), c, maxiter, is_feasible, reginit, tail_at, 1, nullptr,
+                       nullptr, b0, b0 + nb);
+        tpp_compact_count_kernel<<<cb, 1024, 0, st>>>(fin, nb, cnt);
+        tpp_compact_scatter_kernel<<<cb, 1024, 0, st>>>(fin, nb, cnt, d_list + b0, nact, b0);
+        TPP_LAUNCH_BOX(tpp_solve_tail_kernel, ((nb + 31) / 32, 32, 0, st), c, maxiter, is_feasible, reginit, 0, 0, d_list + b0, nact, 0,
+                       nb);
+        last_launches += 4;
+      } else {
+        TPP_LAUNCH_BOX(tpp_solve_kernel, ((nb + 63) / 64, TPP_BLOCK, 0, st), c, maxiter, is_feasible, reginit, 0, 1, nullptr, nullptr,
+                       b0, b0 + nb);
+        ++last_launches;
+      }
       if (ptrace) CGX_CUDA(cudaEventRecord(ptime[k][1], st));
     }
     // second pass in issue order: the copies back are enqueued after EVERY slice's upload and solve, so that no
@@ -269,12 +294,9 @@ struct TppBackend : Backend {
     CGX_CUDA(cudaEventRecord(ev[1], stream));
     auto compaction = [&](int*& d_counts, int*& d_nactive, int& cblocks) {
       cblocks = (c.B + 1023) / 1024;
-      if (!d_list) {
-        d_list = dalloc<int>((size_t)c.Bp + cblocks + 1);
-        allocs.push_back(d_list);
-      }
+      ensure_list();
       d_counts = d_list + c.Bp;
-      d_nactive = d_counts + cblocks;
+      d_nactive = d_counts + cblocks + PIPE_MAX;
     };
     if (chunk > 0 && maxiter > chunk) {
       int *d_counts, *d_nactive, cblocks;
@@ -284,7 +306,7 @@ struct TppBackend : Backend {
       ++last_launches;
       for (int done = chunk; done < maxiter; done += chunk) {
         tpp_compact_count_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts);
-        tpp_compact_scatter_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts, d_list, d_nactive);
+        tpp_compact_scatter_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts, d_list, d_nactive, 0);
         TPP_LAUNCH_BOX(tpp_solve_kernel, (nblocks(), TPP_BLOCK, 0, stream), c, maxiter, is_feasible, reginit, chunk, 0, d_list, d_nactive, 0, c.B);
         last_launches += 3;
       }
@@ -299,7 +321,7 @@ struct TppBackend : Backend {
       const int* fin = c.iscal + (size_t)I_FINISHED * c.Bp;
       TPP_LAUNCH_BOX(tpp_solve_kernel, (nblocks(), TPP_BLOCK, 0, stream), c, maxiter, is_feasible, reginit, tail_at, 1, nullptr, nullptr, 0, c.B);
       tpp_compact_count_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts);
-      tpp_compact_scatter_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts, d_list, d_nactive);
+      tpp_compact_scatter_kernel<<<cblocks, 1024, 0, stream>>>(fin, c.B, d_counts, d_list, d_nactive, 0);
       TPP_LAUNCH_BOX(tpp_solve_tail_kernel, ((c.B + 31) / 32, 32, 0, stream), c, maxiter, is_feasible, reginit, 0, 0, d_list, d_nactive, 0, c.B);
       last_launches += 4;
     } else {

@@ -244,7 +244,7 @@ def test_sliced_host_pipeline_equals_sequential_solve(kind, monkeypatch):
     """cgx_solver_solve_fetch on the thread-per-problem backend cuts the batch into slices on separate streams (copies of
     one slice overlap the solve of the others). Every slice runs the same kernel, so the results must be BIT-identical
     to upload -> solve -> get_all in sequence, for ragged slice sizes too, and equal the oracle on a sample."""
-    B, T = 3 * 1024 + 37, 15  # >= 1024 problems per slice, else the call falls back to the sequence
+    B, T = 4 * 1024 + 37, 15  # >= 1024 problems per slice, else the call falls back to the sequence; >= 4096: two-phase solve in every slice
     x0, problem, solver, ob = _pair(kind, B, T, 77)
     xs = np.repeat(x0[:, None, :], T + 1, 1)
     us = np.zeros((B, T, 2))

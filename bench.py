@@ -161,6 +161,40 @@ class ClockSampler(object):
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Before any pinned allocation: prefer host memory (and, where the cpuset allows it, CPUs) of the NUMA node the
+    rank's GPU hangs off, so that the rank's H2D / D2H traffic does not cross the socket interconnect. Best effort:
+    returns what was found / done for the JSON line."""
+    import ctypes
+    info = {"numa_node": None, "mempolicy": "default", "cpus_bound": False}
+    try:
+        import torch
+        bdf = torch.cuda.get_device_properties(local_rank).pci_bus_id
+        dom = getattr(torch.cuda.get_device_properties(local_rank), "pci_domain_id", 0)
+        dev = getattr(torch.cuda.get_device_properties(local_rank), "pci_device_id", 0)
+        path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (dom, bdf, dev)
+        node = int(open(path).read().strip())
+        info["numa_node"] = node
+        if node < 0:
+            return info
+        libc = ctypes.CDLL(None, use_errno=True)
+        mask = ctypes.c_ulong(1 << node)
+        MPOL_PREFERRED, SYS_set_mempolicy = 1, 238  # x86-64
+        rc = libc.syscall(SYS_set_mempolicy, MPOL_PREFERRED, ctypes.byref(mask), ctypes.c_ulong(64))
+        info["mempolicy"] = "preferred:%d" % node if rc == 0 else "set_mempolicy failed (errno %d)" % ctypes.get_errno()
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        allowed = os.sched_getaffinity(0) & cpus
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            info["cpus_bound"] = True
+    except Exception as e:  # no sysfs / not permitted: run unbound
+        info["error"] = str(e)[:80]
+    return info
+
+
 def hbm_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -357,10 +391,23 @@ class Runner(object):
         cb.check(L.cgx_solver_get_all(h, b"xs", self.dp(chk)))
         if not torch.equal(chk, self.xs_out):
             raise RuntimeError("cgx_solver_solve_fetch: xs_out differs from cgx_solver_get_all(xs)")
+        # host-copy ceiling: the same pinned buffers moved H2D + D2H with nothing else running, all ranks at once
+        d_x = torch.empty_like(self.xs_h, device=self.dev)
+        d_u = torch.empty_like(self.us_h, device=self.dev)
+        self.sync()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            d_x.copy_(self.xs_h, non_blocking=True)
+            d_u.copy_(self.us_h, non_blocking=True)
+            self.xs_out.copy_(d_x, non_blocking=True)
+            self.us_out.copy_(d_u, non_blocking=True)
+        self.sync()
+        copy_ms = 1e3 * (time.perf_counter() - t0) / 3
+        del d_x, d_u
         if dist is not None:
-            v = torch.tensor([dev_ms, e2e_ms, wall_ms], device="cuda", dtype=torch.float64)
+            v = torch.tensor([dev_ms, e2e_ms, wall_ms, copy_ms], device="cuda", dtype=torch.float64)
             dist.all_reduce(v, op=dist.ReduceOp.MAX)
-            dev_ms, e2e_ms, wall_ms = [float(a) for a in v.cpu()]
+            dev_ms, e2e_ms, wall_ms, copy_ms = [float(a) for a in v.cpu()]
         solved = self.total * steps
         kms = float(np.mean(kern_ms))
         h2d = int(self.xs_h.numel() * 8 + self.us_h.numel() * 8)
@@ -370,7 +417,9 @@ class Runner(object):
             "problems_per_gpu": self.B, "problems_total": self.total,
             "e2e": {"value": solved / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / steps,
-                    "host_copy_gbs_per_rank": (h2d + d2h) / (e2e_ms / steps * 1e-3) / 1e9},
+                    "host_copy_gbs_per_rank": (h2d + d2h) / (e2e_ms / steps * 1e-3) / 1e9,
+                    "copy_only_ms_per_step": copy_ms,
+                    "copy_only_gbs_per_rank": 2 * (self.xs_h.numel() + self.us_h.numel()) * 8 / (copy_ms * 1e-3) / 1e9},
             "gpu_launches": int(launches), "clocks": clocks, "wall_ms_per_step": wall_ms / steps,
             "solve_stats": {"iterations_mean": float(records[:, 1].mean()), "converged_frac": float(records[:, 3].mean()),
                             "backward_sweeps_mean": float(nb.mean()), "forward_sweeps_mean": float(nf.mean())},
@@ -439,6 +488,7 @@ def main():
 
     cb.set_device(local_rank)
     torch.cuda.set_device(local_rank)
+    numa = bind_to_gpu_numa_node(local_rank)
     # ---- headline: BASELINE config C2 (or --workload arm) ---------------------------------------------------------
     runner = Runner(wl, rank, local_rank, world, dist, args.batch, args.batch_total)
     B, total = runner.B, runner.total
@@ -460,7 +510,7 @@ def main():
                              "solver state" % ws_gb,
                        "parallelism": "independent OCPs sharded over %d rank(s); NCCL all-gather of per-problem "
                        "{cost,iter,stop,converged}" % world},
-            "e2e": res["e2e"], "gpu_launches": res["gpu_launches"], "clocks": res["clocks"],
+            "e2e": res["e2e"], "host_binding_rank0": numa, "gpu_launches": res["gpu_launches"], "clocks": res["clocks"],
             "wall_ms_per_step": res["wall_ms_per_step"], "solve_stats": res["solve_stats"],
             "roofline": {"kernel": wl.kernel, "bound": "hbm", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,

@@ -140,13 +140,15 @@ __device__ void cta_gemm(double* C, int ldc, const double* A, int lda, const dou
 //   C/D (8x8)   : lane l holds C[l/4][2(l%4)], C[l/4][2(l%4)+1]
 // Out-of-range operands are read as zero, so any M, N, K works. The k-sum is accumulated in groups of four inside the
 // tensor core instead of one DFMA per k: differences from cta_gemm are at rounding level.
+__host__ __device__ inline int cta_mma_tiles(int M, int N) { return ((M + 23) / 24) * ((N + 23) / 24); }
 __device__ __forceinline__ void dmma_8x8x4(double& c0, double& c1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                : "+d"(c0), "+d"(c1)
                : "d"(a), "d"(b));
 }
+// 8 x 16 warp tiles (two accumulator fragments sharing the A fragment): more, smaller tiles — the better fit below n = 48
 template <bool TA>
-__device__ void cta_gemm_mma(double* C, int ldc, const double* A, int lda, const double* B, int ldb, int M, int N, int K,
+__device__ void cta_gemm_mma_8x16(double* C, int ldc, const double* A, int lda, const double* B, int ldb, int M, int N, int K,
                              const double* Add, int ldadd, double alpha) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int tm = (M + 7) >> 3, tn = (N + 15) >> 4;
@@ -192,14 +194,89 @@ __device__ void cta_gemm_mma(double* C, int ldc, const double* A, int lda, const
     }
   }
 }
+
+// Register blocking: one warp owns a 24 x 24 output tile = 3 x 3 fragments, so a k-step of 4 loads 3 A and 3 B
+// fragments from shared memory for 9 DMMAs (0.67 LDS.64 per DMMA; the first version loaded 2 - 3 per DMMA and was bound
+// by the shared-memory pipe: ncu, DMMA pipe 13 % busy). `woff` rotates the tile -> warp assignment so that several
+// products issued between two barriers land on different warps.
+template <bool TA>
+__device__ void cta_gemm_mma(double* C, int ldc, const double* A, int lda, const double* B, int ldb, int M, int N, int K,
+                             const double* Add, int ldadd, double alpha, int woff = 0) {
+  constexpr int RT = 3;  // fragments per tile side
+  const int lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const int warp = ((threadIdx.x >> 5) + nwarps - (woff % nwarps)) % nwarps;
+  const int tm = (M + 8 * RT - 1) / (8 * RT), tn = (N + 8 * RT - 1) / (8 * RT);
+  const int ar = lane >> 2, ac = lane & 3;  // A fragment: row ar, k-offset ac ; B fragment: k-offset ac, column ar
+  for (int tile = warp; tile < tm * tn; tile += nwarps) {
+    const int i0 = (tile % tm) * (8 * RT), j0 = (tile / tm) * (8 * RT);
+    const double* pa[RT];
+    const double* pb[RT];
+    bool oka[RT], okb[RT];
+#pragma unroll
+    for (int r = 0; r < RT; ++r) {
+      const int ia = i0 + 8 * r + ar, jb = j0 + 8 * r + ar;
+      oka[r] = ia < M;
+      okb[r] = jb < N;
+      pa[r] = TA ? (A + (size_t)lda * (oka[r] ? ia : 0)) : (A + (oka[r] ? ia : 0));
+      pb[r] = B + (size_t)ldb * (okb[r] ? jb : 0);
+    }
+    double acc[RT][RT][2];
+#pragma unroll
+    for (int r = 0; r < RT; ++r)
+#pragma unroll
+      for (int q = 0; q < RT; ++q) acc[r][q][0] = acc[r][q][1] = 0.;
+    const int K4 = K & ~3;
+    for (int kk = 0; kk < K4; kk += 4) {
+      const int k = kk + ac;
+      double a[RT], b[RT];
+#pragma unroll
+      for (int r = 0; r < RT; ++r) {
+        a[r] = oka[r] ? (TA ? pa[r][k] : pa[r][(size_t)lda * k]) : 0.;
+        b[r] = okb[r] ? pb[r][k] : 0.;
+      }
+#pragma unroll
+      for (int r = 0; r < RT; ++r)
+#pragma unroll
+        for (int q = 0; q < RT; ++q) dmma_8x8x4(acc[r][q][0], acc[r][q][1], a[r], b[q]);
+    }
+    if (K4 < K) {  // K not a multiple of 4: zero-padded last step
+      const int k = K4 + ac;
+      const bool okk = k < K;
+      double a[RT], b[RT];
+#pragma unroll
+      for (int r = 0; r < RT; ++r) {
+        a[r] = (oka[r] && okk) ? (TA ? pa[r][k] : pa[r][(size_t)lda * k]) : 0.;
+        b[r] = (okb[r] && okk) ? pb[r][k] : 0.;
+      }
+#pragma unroll
+      for (int r = 0; r < RT; ++r)
+#pragma unroll
+        for (int q = 0; q < RT; ++q) dmma_8x8x4(acc[r][q][0], acc[r][q][1], a[r], b[q]);
+    }
+#pragma unroll
+    for (int r = 0; r < RT; ++r) {
+      const int ci = i0 + 8 * r + ar;
+      if (ci >= M) continue;
+#pragma unroll
+      for (int q = 0; q < RT; ++q) {
+        const int cj = j0 + 8 * q + 2 * ac;
+        if (cj < N) C[ci + ldc * cj] = (Add ? Add[ci + ldadd * cj] : 0.) + alpha * acc[r][q][0];
+        if (cj + 1 < N) C[ci + ldc * (cj + 1)] = (Add ? Add[ci + ldadd * (cj + 1)] : 0.) + alpha * acc[r][q][1];
+      }
+    }
+  }
+}
 // dispatcher: tensor cores for the large products, DFMA register tiles otherwise
 template <bool TA>
 __device__ __forceinline__ void cta_gemm_auto(double* C, int ldc, const double* A, int lda, const double* B, int ldb, int M,
-                                              int N, int K, const double* Add, int ldadd, double alpha) {
+                                              int N, int K, const double* Add, int ldadd, double alpha, int woff = 0) {
 #ifndef CGX_NO_DMMA
-  if (K >= 16 && M >= 8 && N >= 8)
-    cta_gemm_mma<TA>(C, ldc, A, lda, B, ldb, M, N, K, Add, ldadd, alpha);
-  else
+  if (K >= 16 && M >= 8 && N >= 8) {
+    if (M >= 48 || N >= 48)
+      cta_gemm_mma<TA>(C, ldc, A, lda, B, ldb, M, N, K, Add, ldadd, alpha, woff);
+    else
+      cta_gemm_mma_8x16<TA>(C, ldc, A, lda, B, ldb, M, N, K, Add, ldadd, alpha);
+  } else
 #endif
     cta_gemm<TA>(C, ldc, A, lda, B, ldb, M, N, K, Add, ldadd, alpha);
 }
@@ -523,7 +600,7 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, i
     __syncthreads();
     // A = Fx^T Vxx' ; G = Fu^T Vxx' ; Qx = Lx + Fx^T Vx' ; Qu = Lu + Fu^T Vx'   (ddp.cpp:204,206,211,214)
     cta_gemm_auto<true>(sm.A, ldn, sm.Fx, ldn, sm.V, ldn, n, n, n, nullptr, 0, 1.);
-    cta_gemm_auto<true>(sm.G, ldm, sm.Fu, ldn, sm.V, ldn, m, n, n, nullptr, 0, 1.);
+    cta_gemm_auto<true>(sm.G, ldm, sm.Fu, ldn, sm.V, ldn, m, n, n, nullptr, 0, 1., cta_mma_tiles(n, n));
     for (int j = tid; j < n + m; j += P) {
       double s = 0.;
       if (j < n) {
@@ -538,8 +615,8 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, i
     __syncthreads();
     // Qxx = Lxx + A Fx (into V: Vxx' is dead) ; Qxu = Lxu + A Fu ; Quu = Luu + G Fu (+ ureg)   (ddp.cpp:202-218)
     cta_gemm_auto<false>(sm.V, ldn, sm.A, ldn, sm.Fx, ldn, n, n, n, nm.Lxx, n, 1.);
-    cta_gemm_auto<false>(sm.Qxu, ldn, sm.A, ldn, sm.Fu, ldn, n, m, n, nm.Lxu, n, 1.);
-    cta_gemm_auto<false>(sm.Quu, ldm, sm.G, ldm, sm.Fu, ldn, m, m, n, nm.Luu, m, 1.);
+    cta_gemm_auto<false>(sm.Qxu, ldn, sm.A, ldn, sm.Fu, ldn, n, m, n, nm.Lxu, n, 1., cta_mma_tiles(n, n));
+    cta_gemm_auto<false>(sm.Quu, ldm, sm.G, ldm, sm.Fu, ldn, m, m, n, nm.Luu, m, 1., cta_mma_tiles(n, n) + cta_mma_tiles(n, m));
     __syncthreads();
     if (has_ureg)
       for (int i = tid; i < m; i += P) sm.Quu[i + ldm * i] += ureg;
@@ -593,7 +670,40 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, i
     }
     __syncthreads();
     if (*sm.flag) return 1;
-    // K = Quu^-1 Qxu^T, k = Quu^-1 Qu: one right-hand side per thread (in-place forward/back substitution)
+    // K = Quu^-1 Qxu^T, k = Quu^-1 Qu: one right-hand side per thread (forward / back substitution in the oracle's
+    // order). m <= 24: the right-hand side lives in registers and only the factor is read from shared memory
+    // (broadcast loads); the in-place version below pays a shared-memory round trip per multiply-add.
+    constexpr int MR = 24;
+    if (m <= MR) {
+      for (int col = tid; col <= n; col += P) {
+        double r[MR];
+#pragma unroll
+        for (int i = 0; i < MR; ++i) r[i] = i < m ? ((col < n) ? sm.Qxu[col + ldn * i] : sm.Qu[i]) : 0.;
+#pragma unroll
+        for (int i = 0; i < MR; ++i) {
+          if (i < m) {
+            double s = r[i];
+#pragma unroll
+            for (int j = 0; j < i; ++j) s -= sm.Lc[i + ldm * j] * r[j];
+            r[i] = s / sm.Lc[i + ldm * i];
+          }
+        }
+#pragma unroll
+        for (int i = MR - 1; i >= 0; --i) {
+          if (i < m) {
+            double s = r[i];
+#pragma unroll
+            for (int j = i + 1; j < MR; ++j)
+              if (j < m) s -= sm.Lc[j + ldm * i] * r[j];
+            r[i] = s / sm.Lc[i + ldm * i];
+          }
+        }
+        double* dst = (col < n) ? (sm.Kg + ldm * col) : sm.kg;
+#pragma unroll
+        for (int i = 0; i < MR; ++i)
+          if (i < m) dst[i] = r[i];
+      }
+    } else
     for (int col = tid; col <= n; col += P) {
       double* r = (col < n) ? (sm.Kg + ldm * col) : sm.kg;
       for (int i = 0; i < m; ++i) r[i] = (col < n) ? sm.Qxu[col + ldn * i] : sm.Qu[i];

@@ -54,6 +54,12 @@ struct CtaBackend : Backend {
     threads = ((tn * tn + 31) / 32) * 32;
     if (threads < M::kMinThreads) threads = M::kMinThreads;
     if (threads > M::kMaxThreads) threads = M::kMaxThreads;
+    // dense nodes on the FP64 tensor-core path: one warp per 24 x 24 tile of the widest phase ([Fx Fu]^T Vxx)
+    if (c.n >= 48 && !cta_is_small(c.n, c.m)) {
+      threads = 32 * cta_mma_tiles(c.n + c.m, c.n);
+      if (threads < M::kMinThreads) threads = M::kMinThreads;
+      if (threads > M::kMaxThreads) threads = M::kMaxThreads;
+    }
     // small nodes: the backward pass is one warp's work (cta_small.cuh), a second warp only halves the resident
     // problems per SM (measured, LQR n = 12, B = 4096: see profiles/r01_riccati_sweep_v3.json)
     if (cta_is_small(c.n, c.m)) threads = 32;

@@ -131,6 +131,10 @@ struct ArmModel {
   __device__ void calcdiff_all(const CtaCtx& c, int b, const double* xs, const double* us) const {
     for (int t = threadIdx.x; t <= c.T; t += blockDim.x) calcdiff_node(c, b, t, xs, us);
   }
+  // calc of one node by the calling thread (thread-per-problem rollout of large batches, cta_forward_thread)
+  __device__ double calc_thread(const double* x, const double* u, double* xnext) const {
+    return arm_calc_node_dev<NV>(u == nullptr ? tparams : params, u == nullptr, x, u, xnext);
+  }
   // calc of one node for the rollout: x, u (null at the terminal node) and xnext in shared memory; warp 0 evaluates
   // it cooperatively (arm_warp.cuh), the other warps of the block wait
   __device__ void calc_block(const double* x, const double* u, double* xnext, double*, double* cost_out) const {

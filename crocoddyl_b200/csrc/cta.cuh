@@ -397,6 +397,7 @@ struct LqrModel {
       calcdiff_serial(xs + (size_t)t * n, t < T ? us + (size_t)t * m : nullptr, c.d_Lx + node * n, c.d_Lu + node * m);
     }
   }
+  __device__ double calc_thread(const double* x, const double* u, double* xnext) const { return calc_serial(x, u, xnext); }
   // calc of one node by the whole block (rollout): x, u in shared memory; writes xnext (shared), returns the
   // cost to thread 0 through *cost_out (shared). scratch: >= 2n+m doubles of shared memory.
   __device__ void calc_block(const double* x, const double* u, double* xnext, double* scratch, double* cost_out) const {
@@ -942,6 +943,85 @@ __device__ int cta_forward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, in
   return 0;
 }
 
+// The same rollout by ONE THREAD per problem, for models with compile-time node sizes (M::kN > 0, the arm). One warp
+// per problem spends most of its lanes waiting on the serial joint recursions of ABA (ncu, B = 8192: 11 of 32 lanes
+// active per instruction, 3980 warp instructions per node, 7.8 ms per trial of the whole batch); with one thread per
+// problem a warp instruction advances 32 rollouts, so a large batch needs ~20x fewer of them. The latency of a lone
+// rollout is about the same, so the host uses this version for large batches only (CtaBackend::solve_phases).
+// Same operation order per problem as cta_forward; the node function is the single-thread M::calc_thread, whose 6x6
+// products are summed in a different order than the warp version's (rounding level, arm_warp.cuh).
+template <class M>
+__device__ int cta_forward_thread(const CtaCtx& c, const M& mod, int b, int cur, double alpha, bool is_feasible,
+                                  double& cost_try_out, double& dv_out, const TrialBufs* tb = nullptr) {
+  constexpr int n = M::kN > 0 ? M::kN : 1, m = M::kM > 0 ? M::kM : 1;
+  const int T = c.T;
+  const bool fddp = c.fddp != 0;
+  const bool closed = !fddp || is_feasible || (alpha == 1.);
+  const bool use_w = fddp && !is_feasible;
+  const double am1 = alpha - 1.;
+  const bool term_open = c.box && !fddp && !(is_feasible || (alpha == 1.));
+  const bool clamp = c.box && c.has_limits[b] != 0;
+  const double* u_lb = c.u_lb + (size_t)b * m;
+  const double* u_ub = c.u_ub + (size_t)b * m;
+  const double* xs = c.xs[cur] + (size_t)b * (T + 1) * n;
+  const double* us = c.us[cur] + (size_t)b * T * m;
+  double* xt_ = (tb ? tb->xs : c.xs[cur ^ 1]) + (size_t)b * (T + 1) * n;
+  double* ut_ = (tb ? tb->us : c.us[cur ^ 1]) + (size_t)b * T * m;
+  double* xnext_ = (tb ? tb->xnext : c.d_xnext) + (size_t)b * (T + 1) * n;
+  double* cost_ = (tb ? tb->cost : c.d_cost) + (size_t)b * (T + 1);
+  const double* fs = c.fs + (size_t)b * (T + 1) * n;
+  const double* w = c.w + (size_t)b * (T + 1) * n;
+  const double* Kb = c.K + (size_t)b * T * m * n;
+  const double* kb = c.k + (size_t)b * T * m;
+  double cost_try = 0., dv = 0.;
+  double xn[n], x[n], dx[n], u[m];
+#pragma unroll
+  for (int i = 0; i < n; ++i) xn[i] = c.x0[(size_t)b * n + i];
+  for (int t = 0; t <= T; ++t) {
+    const bool open = !(closed && !(term_open && t == T));
+#pragma unroll
+    for (int i = 0; i < n; ++i) {
+      const double xt = open ? xn[i] + fs[(size_t)t * n + i] * am1 : xn[i];
+      x[i] = xt;
+      dx[i] = xt - xs[(size_t)t * n + i];
+      xt_[(size_t)t * n + i] = xt;
+    }
+    if (t < T) {
+      const double* Kt = Kb + (size_t)t * m * n;
+#pragma unroll
+      for (int i = 0; i < m; ++i) {
+        double s = 0.;
+#pragma unroll
+        for (int j = 0; j < n; ++j) s += Kt[i + m * j] * dx[j];
+        double uu = us[(size_t)t * m + i] - kb[(size_t)t * m + i] * alpha - s;
+        if (clamp) uu = fmin(fmax(uu, u_lb[i]), u_ub[i]);
+        u[i] = uu;
+        ut_[(size_t)t * m + i] = uu;
+      }
+    }
+    if (use_w) {
+      double s = 0.;
+#pragma unroll
+      for (int i = 0; i < n; ++i) s += w[(size_t)t * n + i] * dx[i];
+      dv += s;
+    }
+    const double cst = mod.calc_thread(x, t < T ? u : nullptr, xn);
+#pragma unroll
+    for (int i = 0; i < n; ++i) xnext_[(size_t)t * n + i] = xn[i];
+    cost_[t] = cst;
+    cost_try += cst;
+    bool bad = raise_if_nan(cost_try);
+    if (t < T) {
+#pragma unroll
+      for (int i = 0; i < n; ++i) bad = bad || raise_if_nan(fabs(xn[i]));
+    }
+    if (bad) return 1;
+  }
+  cost_try_out = cost_try;
+  dv_out = dv;
+  return 0;
+}
+
 __device__ inline bool cta_accept(const SolverOpts& o, bool fddp, bool is_feasible, double d0, double dV, double dVexp) {
   if (fddp) {
     if (dVexp >= 0) return d0 < o.th_grad || dV > o.th_acceptstep * dVexp;
@@ -1274,6 +1354,22 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kFwdMinBlocks) cta_phase_fo
   if (threadIdx.x == 0) cta_phase_trial_done(c, b, maxiter, st, cost_try, dv);
 }
 
+// the same phase with one thread per problem (cta_forward_thread): large batches of compile-time-sized models
+template <class M>
+__global__ void __launch_bounds__(32) cta_phase_forward_tpp_kernel(const __grid_constant__ CtaCtx c, int maxiter) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= c.B) return;
+  if (CTA_I(I_PHASE) != 1) return;
+  M mod;
+  mod.load(c, b);
+  const int cur = CTA_I(I_CUR);
+  const bool feas = CTA_I(I_FEAS) != 0;
+  const double steplength = c.o.alphas[CTA_I(I_ALPHA)];
+  double cost_try = 0., dv = 0.;
+  const int st = cta_forward_thread(c, mod, b, cur, steplength, feas, cost_try, dv);
+  cta_phase_trial_done(c, b, maxiter, st, cost_try, dv);
+}
+
 // Concurrent line search (the trials of one iteration are independent given xs, us, K, k): block (b, g)
 // rolls out step length index I_ALPHA + g of problem b. Slot 0 writes the problem's own trial buffers, slot g > 0 the
 // g-th spare set; nothing of the solver state changes here. cta_phase_select_kernel then walks the slots in the
@@ -1309,6 +1405,24 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kFwdMinBlocks) cta_phase_fo
     r[(size_t)c.Bp + b] = cost_try;
     r[(size_t)2 * c.Bp + b] = dv;
   }
+}
+template <class M>
+__global__ void __launch_bounds__(32) cta_phase_forward_wide_tpp_kernel(const __grid_constant__ CtaCtx c, const __grid_constant__ TrialSlots ts) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x, g = blockIdx.y;
+  if (b >= c.B) return;
+  if (CTA_I(I_PHASE) != 1) return;
+  const int a = CTA_I(I_ALPHA) + g;
+  if (a >= c.o.nalphas) return;
+  M mod;
+  mod.load(c, b);
+  const int cur = CTA_I(I_CUR);
+  const bool feas = CTA_I(I_FEAS) != 0;
+  double cost_try = 0., dv = 0.;
+  const int st = cta_forward_thread(c, mod, b, cur, c.o.alphas[a], feas, cost_try, dv, g ? &ts.spare[g - 1] : nullptr);
+  double* r = ts.res + (size_t)g * 3 * c.Bp;
+  r[b] = st;
+  r[(size_t)c.Bp + b] = cost_try;
+  r[(size_t)2 * c.Bp + b] = dv;
 }
 static __global__ void cta_phase_select_kernel(const __grid_constant__ CtaCtx c, const __grid_constant__ TrialSlots ts, int maxiter) {
   const int b = blockIdx.x;

@@ -238,6 +238,12 @@ struct CtaBackend : Backend {
     const double span = std::log(std::max(c.o.regmax, 1e-300) / std::max(c.o.regmin, 1e-300)) / std::log(c.o.regfactor);
     const long max_retries = (long)std::ceil(std::max(span, 0.)) + 2;
     const long max_rounds = (long)maxiter * (c.o.nalphas + max_retries) + RING;
+    // rollout by one thread per problem (cta_forward_thread) while many problems are unfinished: a warp instruction then
+    // advances 32 rollouts instead of one. A lone rollout is ~1.5x slower that way, so the warp version takes over for
+    // the tail (measured, arm C4: 143 ms with warps, 187 ms with threads). The two node functions differ at rounding
+    // level (arm_warp.cuh); the sequence of counts, and so the schedule, is deterministic for a given batch.
+    int tpp_min = 1536;
+    if (const char* e = getenv("CGX_CTA_TPP_FORWARD_MIN")) tpp_min = atoi(e);
     long unfinished = c.B;  // last count that came back (never smaller than the truth)
     long last_round = -1;
     bool finished = false;
@@ -255,6 +261,7 @@ struct CtaBackend : Backend {
       // concurrent line search while all trials of the unfinished problems fit the GPU in one wave (cta.cuh)
       const bool wide = wide_mode == 1 || (wide_mode < 0 && unfinished * CTA_LS_WIDTH <= (long)num_sms * M::kFwdMinBlocks);
       if (wide) ensure_trial_slots();
+      const bool tpp_forward = M::kN > 0 && unfinished >= tpp_min;
       CGX_CUDA(cudaMemsetAsync(d_active + slot, 0, sizeof(int), stream));
       if constexpr (M::kNodeKernel) {
         const long nodes = (long)c.B * (c.T + 1);
@@ -263,9 +270,14 @@ struct CtaBackend : Backend {
       }
       cta_phase_direction_kernel<M><<<c.B, threads, smem, stream>>>(c, d_active + slot);
       if (wide) {
-        cta_phase_forward_wide_kernel<M><<<dim3(c.B, CTA_LS_WIDTH), threads, cta_blockwide_smem_bytes(c.n, c.m), stream>>>(c, slots);
+        if (tpp_forward)
+          cta_phase_forward_wide_tpp_kernel<M><<<dim3((c.B + 31) / 32, CTA_LS_WIDTH), 32, 0, stream>>>(c, slots);
+        else
+          cta_phase_forward_wide_kernel<M><<<dim3(c.B, CTA_LS_WIDTH), threads, cta_blockwide_smem_bytes(c.n, c.m), stream>>>(c, slots);
         cta_phase_select_kernel<<<c.B, 128, 0, stream>>>(c, slots, maxiter);
         ++last_launches;
+      } else if (tpp_forward) {
+        cta_phase_forward_tpp_kernel<M><<<(c.B + 31) / 32, 32, 0, stream>>>(c, maxiter);
       } else {
         cta_phase_forward_kernel<M><<<c.B, threads, cta_blockwide_smem_bytes(c.n, c.m), stream>>>(c, maxiter);
       }

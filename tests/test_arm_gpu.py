@@ -149,6 +149,36 @@ def test_solve_same_iterations_and_accept_sequence(solver_kind, kind, nv, T):
         np.testing.assert_allclose(tg[:, 1], to[:, 1], rtol=1e-9)  # cost per iteration
 
 
+@pytest.mark.parametrize("solver_kind", ["fddp", "ddp"])
+@pytest.mark.parametrize("wide", ["0", "1"])
+def test_thread_per_problem_rollout_of_large_batches(solver_kind, wide, monkeypatch):
+    """Batches of >= 2048 arm problems roll out with one thread per problem (cta_forward_thread) instead of one warp:
+    forced here on a small batch (CGX_CTA_TPP_FORWARD_MIN), sequential and concurrent line search. Same decisions as
+    the oracle in every iteration; the single-thread node function sums its 6x6 products in another order than the
+    warp version, so values are compared at the usual tolerances, not bitwise with the warp schedule."""
+    monkeypatch.setenv("CGX_CTA_TPP_FORWARD_MIN", "1")
+    monkeypatch.setenv("CGX_CTA_WIDE", wide)
+    model = _model("synthetic", 7, seed=9)
+    B, T = 37, 30
+    x0, xs = _c4_inputs(model, B, T)
+    problem, solver, ob = _pair(solver_kind, model, x0, T)
+    us = np.repeat(problem.quasiStatic(x0)[:, None, :], T, 1)
+    solver.enableTrace(100)
+    conv = solver.solve(xs, us, 100, False, 0.1)
+    ob.solve(xs, us, 100, False, 0.1)
+    _compare_solve(solver, ob, conv, rtol=1e-7)
+    for b in range(0, B, 5):
+        tg, to = solver.trace(b), ob.trace(b)
+        assert tg.shape == to.shape
+        for col in (0, 5, 6, 7, 8, 11, 12):
+            assert np.array_equal(tg[:, col], to[:, col]), (b, col)
+        np.testing.assert_allclose(tg[:, 1], to[:, 1], rtol=1e-9)
+    # node data left by the accepted rollout (datas[t]->xnext / cost) are those of the final trajectory
+    xsg, usg = solver.get("xs"), solver.get("us")
+    cost = problem.calc(xsg, usg)
+    np.testing.assert_allclose(cost, solver.scalars()["cost"], rtol=1e-9)
+
+
 def test_config_c4_full_horizon_sampled_against_oracle():
     """BASELINE config C4 shape (7-DoF synthetic arm, T = 100, FDDP, reginit 0.1) on a batch, a sample of which is
     solved by the oracle; plus size-independent properties on the whole batch."""

@@ -192,6 +192,55 @@ __device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, int cur, 
       if (t > 0) load_node(t - 1, S + (((T - t + 1) & 1) ? pl.stage_sz : 0));
       const double* F = mb + pl.oFx;  // [Fx Fu], n x (n+m), leading dimension ldn
       // P1: [A; G | Qx; Qu] = [Fx Fu]^T [Vxx' Vx']   (ddp.cpp:204,206,211,214)
+      if constexpr (KN > 0 && KM > 0 && KN == 2 * KM) {
+        // register tiles: lane (rg, cg) owns rows {3 rg .. 3 rg + 2} x columns {TC cg ..} of the (n + m) x (n + 1)
+        // product, so a k-step loads 3 + TC operands for 3 TC multiply-adds (the strided version below loads 2 per
+        // multiply-add and was bound by the shared-memory pipe: ncu, FP64 pipe 10 %). Each output still sums over k
+        // ascending: same values.
+        constexpr int RG = KM, CG = 32 / RG, TR = 3, NC = KN + 1, TC = (NC + CG - 1) / CG;
+        const int rg = lane % RG, cg = lane / RG;
+        if (cg < CG) {
+          double acc[TR][TC];
+          int fo[TR], vo[TC];
+#pragma unroll
+          for (int a = 0; a < TR; ++a) fo[a] = ldn * (TR * rg + a);
+#pragma unroll
+          for (int bb = 0; bb < TC; ++bb) vo[bb] = ldn * min(TC * cg + bb, NC - 1);
+#pragma unroll
+          for (int a = 0; a < TR; ++a)
+#pragma unroll
+            for (int bb = 0; bb < TC; ++bb) acc[a][bb] = 0.;
+#pragma unroll
+          for (int k = 0; k < KN; ++k) {
+            double fv[TR], vv[TC];
+#pragma unroll
+            for (int a = 0; a < TR; ++a) fv[a] = F[fo[a] + k];
+#pragma unroll
+            for (int bb = 0; bb < TC; ++bb) vv[bb] = V[vo[bb] + k];
+#pragma unroll
+            for (int a = 0; a < TR; ++a)
+#pragma unroll
+              for (int bb = 0; bb < TC; ++bb) acc[a][bb] += fv[a] * vv[bb];
+          }
+#pragma unroll
+          for (int a = 0; a < TR; ++a)
+#pragma unroll
+            for (int bb = 0; bb < TC; ++bb) {
+              const int i = TR * rg + a, j = TC * cg + bb;
+              if (j >= NC) continue;
+              if (j < n) {
+                if (i < n)
+                  A[i + ldn * j] = acc[a][bb];
+                else
+                  G[(i - n) + ldm * j] = acc[a][bb];
+              } else if (i < n) {
+                Qx[i] = st[pl.oLx + i] + acc[a][bb];
+              } else {
+                Qu[i - n] = st[pl.oLu + i - n] + acc[a][bb];
+              }
+            }
+        }
+      } else
       {
         const int R1 = n + m, NO = R1 * (n + 1);
         double acc[O1];
@@ -257,18 +306,59 @@ __device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, int cur, 
             acu[q] = 0.;
           }
         }
+        constexpr bool TILED = KN > 0 && KM > 0 && KN == 2 * KM;
 #pragma unroll
         for (int k = 0; k < (KN ? KN : 16); ++k) {
           if (!KN && k >= n) break;
+          if constexpr (!TILED) {
 #pragma unroll
-          for (int q = 0; q < O2; ++q) acc[q] += A[ao[q] + ldn * k] * F[fo[q] + k];
+            for (int q = 0; q < O2; ++q) acc[q] += A[ao[q] + ldn * k] * F[fo[q] + k];
+          }
 #pragma unroll
           for (int q = 0; q < O3; ++q) acu[q] += G[go[q] + ldm * k] * F[fu[q] + k];
+        }
+        if constexpr (TILED) {
+          // [Qxx Qxu] = [Lxx Lxu] + A [Fx Fu]: lane (rg, cg) owns rows {2 rg, 2 rg + 1} x TC columns of n x (n + m)
+          constexpr int RG = KM, CG = 32 / RG, TR = 2, NC = KN + KM, TC = (NC + CG - 1) / CG;
+          const int rg = lane % RG, cg = lane / RG;
+          if (cg < CG) {
+            double t[TR][TC];
+            int fo2[TC];
+#pragma unroll
+            for (int bb = 0; bb < TC; ++bb) fo2[bb] = ldn * min(TC * cg + bb, NC - 1);
+#pragma unroll
+            for (int a = 0; a < TR; ++a)
+#pragma unroll
+              for (int bb = 0; bb < TC; ++bb) t[a][bb] = 0.;
+#pragma unroll
+            for (int k = 0; k < KN; ++k) {
+              double av[TR], fv[TC];
+#pragma unroll
+              for (int a = 0; a < TR; ++a) av[a] = A[TR * rg + a + ldn * k];
+#pragma unroll
+              for (int bb = 0; bb < TC; ++bb) fv[bb] = F[fo2[bb] + k];
+#pragma unroll
+              for (int a = 0; a < TR; ++a)
+#pragma unroll
+                for (int bb = 0; bb < TC; ++bb) t[a][bb] += av[a] * fv[bb];
+            }
+#pragma unroll
+            for (int a = 0; a < TR; ++a)
+#pragma unroll
+              for (int bb = 0; bb < TC; ++bb) {
+                const int i = TR * rg + a, j = TC * cg + bb;
+                if (j >= NC) continue;
+                if (j < n)
+                  V[i + ldn * j] = mb[pl.oLxx + i + ldn * j] + t[a][bb];
+                else
+                  Qxu[i + ldn * (j - n)] = (has_Lxu ? mb[pl.oLxu + i + ldn * (j - n)] : 0.) + t[a][bb];
+              }
+          }
         }
         ColMajorIter it(lane, n);
 #pragma unroll
         for (int q = 0; q < O2; ++q, it.next()) {
-          if (lane + 32 * q >= NO) break;
+          if (TILED || lane + 32 * q >= NO) break;
           const int i = it.r, j = it.c;
           if (j < n)
             V[i + ldn * j] = mb[pl.oLxx + i + ldn * j] + acc[q];
@@ -429,7 +519,40 @@ __device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, int cur, 
         }
         Vx[lane] = v;
       }
-      {
+      if constexpr (KN > 0 && KM > 0 && KN == 2 * KM) {
+        // Vxx = Qxx - Qxu K: lane (rg, cg) owns rows {2 rg, 2 rg + 1} x TC columns of n x n
+        constexpr int RG = KM, CG = 32 / RG, TR = 2, TC = (KN + CG - 1) / CG;
+        const int rg = lane % RG, cg = lane / RG;
+        if (cg < CG) {
+          double t[TR][TC];
+          int ko2[TC];
+#pragma unroll
+          for (int bb = 0; bb < TC; ++bb) ko2[bb] = ldm * min(TC * cg + bb, KN - 1);
+#pragma unroll
+          for (int a = 0; a < TR; ++a)
+#pragma unroll
+            for (int bb = 0; bb < TC; ++bb) t[a][bb] = 0.;
+#pragma unroll
+          for (int k = 0; k < KM; ++k) {
+            double qv[TR], kv[TC];
+#pragma unroll
+            for (int a = 0; a < TR; ++a) qv[a] = Qxu[TR * rg + a + ldn * k];
+#pragma unroll
+            for (int bb = 0; bb < TC; ++bb) kv[bb] = Kg[ko2[bb] + k];
+#pragma unroll
+            for (int a = 0; a < TR; ++a)
+#pragma unroll
+              for (int bb = 0; bb < TC; ++bb) t[a][bb] += qv[a] * kv[bb];
+          }
+#pragma unroll
+          for (int a = 0; a < TR; ++a)
+#pragma unroll
+            for (int bb = 0; bb < TC; ++bb) {
+              const int i = TR * rg + a, j = TC * cg + bb;
+              if (j < KN) V[i + ldn * j] = V[i + ldn * j] + -1. * t[a][bb];
+            }
+        }
+      } else {
         double acc[O5];
         int qo[O5], ko[O5];
         {

@@ -75,7 +75,10 @@ SIGNATURES = {
     "cgx_solver_set_callback": (C.c_int, [_vp, CALLBACK, _vp]),
     "cgx_solver_last_timing": (C.c_int, [_vp, _dp, _ip]),
     "cgx_probe_fp64_tflops": (C.c_int, [_dp]),
+    "cgx_unicycle_calc_noalloc": (C.c_int, [C.c_int, C.c_int, _dp, _dp, _dp, _dp, _dp]),
 }
+
+NOALLOC_SCRATCH_DOUBLES = 1048576  # CGX_NOALLOC_SCRATCH_DOUBLES
 
 NSCALARS = 17
 NTRACE = 13

@@ -15,7 +15,7 @@ LIB = os.path.join(LIBDIR, "libcrocoddyl_b200.so")
 # per-source extra flags (none: the register budget of the thread-per-problem solve kernel — 128, so that 65,536 problems
 # are resident in ONE wave — is set by its __launch_bounds__, and its tail instantiation deliberately has none)
 EXTRA = {}
-SOURCES = ["cta_arm7.cu", "cta_arm4.cu", "cta_arm2.cu", "cta_backend.cu", "tpp_backend.cu", "capi.cu"]
+SOURCES = ["cta_arm7.cu", "cta_arm4.cu", "cta_arm2.cu", "cta_backend.cu", "tpp_backend.cu", "capi.cu", "noalloc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-Xcompiler", "-fvisibility=hidden"]
 

@@ -150,6 +150,11 @@ void fetch_scalars(cgx_solver_s* s) {
 
 }  // namespace
 
+// for the other translation units of the library (noalloc.cu): store the message cgx_last_error() returns
+namespace cgx {
+int set_last_error(int code, const std::string& msg) { return fail(code, msg); }
+}  // namespace cgx
+
 extern "C" {
 
 const char* cgx_last_error(void) { return g_err.c_str(); }

@@ -226,6 +226,23 @@ CGX_API int cgx_solver_last_timing(cgx_solver_t s, double* ms, int* launches);
  * the FP64 peak is not in MEASURED_PEAKS.json). Returns achieved TFLOP/s of a register-resident DFMA loop. */
 CGX_API int cgx_probe_fp64_tflops(double* tflops);
 
+/* ----------------------------------------------------------------------------------------------
+ * cgx_unicycle_calc_noalloc — NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * ShootingProblem::calc for B unicycle problems (what cgx_problem_calc returns for CGX_MODEL_UNICYCLE: costs[b] = total
+ * cost of xs[b], us[b]) without creating a handle and without any cudaMalloc / cudaFree / stream / event: the staging of
+ * xs / us and the per-node costs between the node kernel and the reduction live in ONE static device array of
+ * CGX_NOALLOC_SCRATCH_DOUBLES doubles (8 MiB per GPU that loads the library, held until exit).
+ *   params  = [dt, w_x, w_u] of the running model, tparams = the terminal model's (NULL: the running model's);
+ *   xs = [B][T+1][3], us = [B][T][2], costs = [B]; host or device pointers (copied with cudaMemcpyDefault);
+ *   runs on the current device's legacy default stream and returns after the result has arrived.
+ * Limit: B * (6 T + 5) <= CGX_NOALLOC_SCRATCH_DOUBLES (e.g. B <= 1733 at T = 100), else CGX_ERR_INVALID — nothing is
+ * allocated to make room. Every call shares the array (it keeps the last call's contents; a call writes every word
+ * before reading it, nothing needs clearing): calls that overlap on the GPU race on it — serialise them. */
+#define CGX_NOALLOC_SCRATCH_DOUBLES 1048576
+CGX_API int cgx_unicycle_calc_noalloc(int B, int T, const double* params, const double* tparams, const double* xs,
+                                      const double* us, double* costs);
+
 #ifdef __cplusplus
 }
 #endif

@@ -82,7 +82,9 @@ class Arm(object):
     oracle_kind = "arm"
     n, m = 14, 7
     # FP64 work per node: Riccati F_ric(14,7); calc / calcDiff = static operation count of the node functions
-    # (tools/count_fp64_ops.py: DFMA = 2, DADD = DMUL = 1 flop)
+    # (tools/count_fp64_ops.py: DFMA = 2, DADD = DMUL = 1 flop). The dense statement of the same algorithms run on a counting
+    # scalar executes more (12,666 / 40,096: profiles/r02_arm_flops_counting_scalar.json); the smaller, issued figure is
+    # the one used, so that the fraction is not inflated by work the kernel does not do.
     flops_ric = 4 * n**3 + 6 * n * n * m + 4 * n * m * m + m**3 / 3. + 6 * n * n + 6 * n * m + 4 * m * m
     flops_calc, flops_calcdiff = 7375., 22173.
     # CTA-per-problem core: node derivatives are written by calcDiff and read back by the backward pass

@@ -81,6 +81,12 @@ class ActionModelLQR(ActionModelAbstract):
         return p[0] if B is None else p
 
 
+from .integrated import (DifferentialActionModelFreeFwdDynamics, DifferentialActionModelLQR,  # noqa: E402,F401
+                         make_integrated_euler)
+
+IntegratedActionModelEuler = make_integrated_euler(ActionModelLQR)
+
+
 class ShootingProblem(object):
     """ShootingProblem(x0, runningModels, terminalModel) (include/crocoddyl/core/optctrl/shooting.hpp:48-63).
 
@@ -134,7 +140,7 @@ class ShootingProblem(object):
 
     def __del__(self):
         h = getattr(self, "_h", None)
-        if h:
+        if h and lib is not None:  # module globals are already gone at interpreter shutdown
             lib().cgx_problem_destroy(h)
             self._h = None
 
@@ -258,7 +264,7 @@ class SolverDDP(object):
 
     def __del__(self):
         h = getattr(self, "_h", None)
-        if h:
+        if h and lib is not None:  # module globals are already gone at interpreter shutdown
             lib().cgx_solver_destroy(h)
             self._h = None
 

@@ -538,6 +538,40 @@ __device__ double cta_calcdiff(const CtaCtx& c, const M& mod, CtaSmem& sm, int b
   return sm.red[0];
 }
 
+// K = Quu^-1 Qxu^T, k = Quu^-1 Qu with the right-hand side of a thread in registers (m <= MR): only the factor is read
+// from shared memory (broadcast loads). Same operation order as the in-place version in cta_backward.
+template <int MR>
+__device__ __forceinline__ void cta_solve_rhs_regs(CtaSmem& sm, int n, int m, int ldn, int ldm, int tid, int P) {
+  for (int col = tid; col <= n; col += P) {
+    double r[MR];
+#pragma unroll
+    for (int i = 0; i < MR; ++i) r[i] = i < m ? ((col < n) ? sm.Qxu[col + ldn * i] : sm.Qu[i]) : 0.;
+#pragma unroll
+    for (int i = 0; i < MR; ++i) {
+      if (i < m) {
+        double s = r[i];
+#pragma unroll
+        for (int j = 0; j < i; ++j) s -= sm.Lc[i + ldm * j] * r[j];
+        r[i] = s / sm.Lc[i + ldm * i];
+      }
+    }
+#pragma unroll
+    for (int i = MR - 1; i >= 0; --i) {
+      if (i < m) {
+        double s = r[i];
+#pragma unroll
+        for (int j = i + 1; j < MR; ++j)
+          if (j < m) s -= sm.Lc[j + ldm * i] * r[j];
+        r[i] = s / sm.Lc[i + ldm * i];
+      }
+    }
+    double* dst = (col < n) ? (sm.Kg + ldm * col) : sm.kg;
+#pragma unroll
+    for (int i = 0; i < MR; ++i)
+      if (i < m) dst[i] = r[i];
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // SolverDDP::backwardPass + computeGains (ddp.cpp:180-253,298-310) for one problem by the whole block, with the
 // reductions of updateExpectedImprovement (fddp.cpp:126-147) / expectedImprovement (ddp.cpp:144-155) /
@@ -674,37 +708,15 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, i
     // K = Quu^-1 Qxu^T, k = Quu^-1 Qu: one right-hand side per thread (forward / back substitution in the oracle's
     // order). m <= 24: the right-hand side lives in registers and only the factor is read from shared memory
     // (broadcast loads); the in-place version below pays a shared-memory round trip per multiply-add.
-    constexpr int MR = 24;
-    if (m <= MR) {
-      for (int col = tid; col <= n; col += P) {
-        double r[MR];
-#pragma unroll
-        for (int i = 0; i < MR; ++i) r[i] = i < m ? ((col < n) ? sm.Qxu[col + ldn * i] : sm.Qu[i]) : 0.;
-#pragma unroll
-        for (int i = 0; i < MR; ++i) {
-          if (i < m) {
-            double s = r[i];
-#pragma unroll
-            for (int j = 0; j < i; ++j) s -= sm.Lc[i + ldm * j] * r[j];
-            r[i] = s / sm.Lc[i + ldm * i];
-          }
-        }
-#pragma unroll
-        for (int i = MR - 1; i >= 0; --i) {
-          if (i < m) {
-            double s = r[i];
-#pragma unroll
-            for (int j = i + 1; j < MR; ++j)
-              if (j < m) s -= sm.Lc[j + ldm * i] * r[j];
-            r[i] = s / sm.Lc[i + ldm * i];
-          }
-        }
-        double* dst = (col < n) ? (sm.Kg + ldm * col) : sm.kg;
-#pragma unroll
-        for (int i = 0; i < MR; ++i)
-          if (i < m) dst[i] = r[i];
-      }
-    } else
+    if (m <= 8)
+      cta_solve_rhs_regs<8>(sm, n, m, ldn, ldm, tid, P);
+    else if (m <= 12)
+      cta_solve_rhs_regs<12>(sm, n, m, ldn, ldm, tid, P);
+    else if (m <= 16)
+      cta_solve_rhs_regs<16>(sm, n, m, ldn, ldm, tid, P);
+    else if (m <= 24)
+      cta_solve_rhs_regs<24>(sm, n, m, ldn, ldm, tid, P);
+    else
     for (int col = tid; col <= n; col += P) {
       double* r = (col < n) ? (sm.Kg + ldm * col) : sm.kg;
       for (int i = 0; i < m; ++i) r[i] = (col < n) ? sm.Qxu[col + ldn * i] : sm.Qu[i];

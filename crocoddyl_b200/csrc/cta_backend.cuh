@@ -5,7 +5,9 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
+#include <vector>
 #include "backend.hpp"
 #include "cta.cuh"
 
@@ -247,6 +249,18 @@ struct CtaBackend : Backend {
     long unfinished = c.B;  // last count that came back (never smaller than the truth)
     long last_round = -1;
     bool finished = false;
+    // development aid: CGX_CTA_PHASE_TIMING=1 prints, per round, the unfinished count the host knew and the duration
+    // of the three phases (timing events on the solve stream; nothing is recorded otherwise)
+    static const bool phase_timing = getenv("CGX_CTA_PHASE_TIMING") && getenv("CGX_CTA_PHASE_TIMING")[0] == '1';
+    std::vector<cudaEvent_t> pt_ev;
+    std::vector<long> pt_unf;
+    auto pt_mark = [&]() {
+      if (!phase_timing) return;
+      cudaEvent_t e;
+      CGX_CUDA(cudaEventCreate(&e));
+      CGX_CUDA(cudaEventRecord(e, stream));
+      pt_ev.push_back(e);
+    };
     for (long r = 0; r < max_rounds; ++r) {
       const int slot = (int)(r % RING);
       if (r >= RING - 1) {  // result of round r - (RING - 1)
@@ -263,12 +277,16 @@ struct CtaBackend : Backend {
       if (wide) ensure_trial_slots();
       const bool tpp_forward = M::kN > 0 && unfinished >= tpp_min;
       CGX_CUDA(cudaMemsetAsync(d_active + slot, 0, sizeof(int), stream));
+      pt_unf.push_back(unfinished);
+      pt_mark();
       if constexpr (M::kNodeKernel) {
         const long nodes = (long)c.B * (c.T + 1);
         cta_phase_nodes_kernel<M><<<(unsigned)((nodes + 63) / 64), 64, 0, stream>>>(c);
         ++last_launches;
       }
+      pt_mark();
       cta_phase_direction_kernel<M><<<c.B, threads, smem, stream>>>(c, d_active + slot);
+      pt_mark();
       if (wide) {
         if (tpp_forward)
           cta_phase_forward_wide_tpp_kernel<M><<<dim3((c.B + 31) / 32, CTA_LS_WIDTH), 32, 0, stream>>>(c, slots);
@@ -282,9 +300,26 @@ struct CtaBackend : Backend {
         cta_phase_forward_kernel<M><<<c.B, threads, cta_blockwide_smem_bytes(c.n, c.m), stream>>>(c, maxiter);
       }
       last_launches += 2;
+      pt_mark();
       CGX_CUDA(cudaMemcpyAsync(h_active + slot, d_active + slot, sizeof(int), cudaMemcpyDeviceToHost, stream));
       CGX_CUDA(cudaEventRecord(ring_ev[slot], stream));
       last_round = r;
+    }
+    if (phase_timing) {
+      CGX_CUDA(cudaStreamSynchronize(stream));
+      double tot[3] = {0., 0., 0.};
+      for (size_t r = 0; r * 4 + 3 < pt_ev.size(); ++r) {
+        float ms[3];
+        for (int k = 0; k < 3; ++k) {
+          CGX_CUDA(cudaEventElapsedTime(&ms[k], pt_ev[r * 4 + k], pt_ev[r * 4 + k + 1]));
+          tot[k] += ms[k];
+        }
+        fprintf(stderr, "[cgx phases] round %3zu unfinished<=%6ld nodes %.3f direction %.3f forward %.3f ms\n", r, pt_unf[r],
+                ms[0], ms[1], ms[2]);
+      }
+      fprintf(stderr, "[cgx phases] total nodes %.2f direction %.2f forward %.2f ms over %zu rounds\n", tot[0], tot[1], tot[2],
+              pt_ev.size() / 4);
+      for (cudaEvent_t e : pt_ev) cudaEventDestroy(e);
     }
     if (!finished) {  // the round bound was hit: make sure that every problem has returned (backstop)
       CGX_CUDA(cudaStreamSynchronize(stream));

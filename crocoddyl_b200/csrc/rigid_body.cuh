@@ -835,6 +835,9 @@ CGX_HD void arm_calcdiff_node(const ArmParams& P, bool terminal, const double* x
     double tau[NV];
     rnea<NV>(P, x, x + NV, a, tau, k, d, true);
   }
+#if defined(CGX_RB_COL_NOUNROLL)
+#pragma unroll 1
+#endif
   for (int kc = 0; kc < NV; ++kc) {
     double tq[NV], tv[NV];
     rnea_derivative_column<NV>(P, k, d, x + NV, kc, tq, tv);

@@ -1267,6 +1267,23 @@ __global__ void tpp_gather_kernel(double* user, double* base0, double* base1, co
     for (int e = 0; e < fm.size; ++e) up[e] = rec[fm.off[e]];
   }
 }
+// Records of the LISTED problems -> the caller's array, one block per listed problem, consecutive threads writing
+// consecutive doubles of that problem's [nt][size] block (coalesced: the destination may be page-locked HOST memory
+// written through the unified address space, TppBackend::solve_pipelined). list holds global problem indices.
+__global__ void tpp_gather_list_kernel(double* user, const double* base0, const double* base1, const int* sel, int flip,
+                                       TppFieldMap fm, int Bp, const int* __restrict__ list, const int* __restrict__ nlist) {
+  const int n = *nlist;
+  const int per = fm.nt * fm.size;
+  for (int j = blockIdx.x; j < n; j += gridDim.x) {
+    const int b = list[j];
+    const double* base = (sel && ((sel[b] ^ flip) & 1)) ? base1 : base0;
+    double* up = user + (size_t)b * per;
+    for (int i = threadIdx.x; i < per; i += blockDim.x) {
+      const int t = i / fm.size, e = i - t * fm.size;
+      up[i] = base[((size_t)t * Bp + b) * fm.R + fm.off[e]];
+    }
+  }
+}
 // x0: host [B][N] -> [N][Bp]
 __global__ void tpp_x0_kernel(const double* user, double* x0, int N, int B, int Bp) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;

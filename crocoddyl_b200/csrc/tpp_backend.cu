@@ -178,7 +178,9 @@ struct TppBackend : Backend {
   // CROCODDYL_B200_TPP_PIPELINE=<K> (default 4; 0/1 = off, the caller then uses upload / solve / get_all in sequence).
   static constexpr int PIPE_MAX = 8;
   cudaStream_t pstream[PIPE_MAX] = {};
+  cudaStream_t dstream[PIPE_MAX] = {};  // early download of a slice while its tail kernel runs
   cudaEvent_t pev[PIPE_MAX] = {};
+  cudaEvent_t pev_phase1[PIPE_MAX] = {}, pev_early[PIPE_MAX] = {};
   cudaEvent_t ev_reset = nullptr;
   cudaEvent_t ptime[PIPE_MAX][3] = {};  // CROCODDYL_B200_TPP_PIPELINE_TRACE=1: upload done / solve done / download done
   double* d_out_xs = nullptr;
@@ -187,6 +189,16 @@ struct TppBackend : Backend {
     const char* e = getenv("CROCODDYL_B200_TPP_PIPELINE");
     const int k = e ? atoi(e) : 4;
     return k > PIPE_MAX ? PIPE_MAX : k;
+  }
+  // device-usable address of a page-locked host buffer (unified addressing), or null if p is pageable / device memory
+  static double* mapped_host(double* p) {
+    if (!p) return nullptr;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+      cudaGetLastError();
+      return nullptr;
+    }
+    return at.type == cudaMemoryTypeHost ? (double*)at.devicePointer : nullptr;
   }
   bool solve_pipelined(const double* h_xs, const double* h_us, double* d_xs, double* d_us, int maxiter,
                        int is_feasible, double reginit, double* h_xs_out, double* h_us_out) override {
@@ -217,6 +229,24 @@ struct TppBackend : Backend {
     const int tail_at = tail_iter();
     const bool two_phase = tail_at > 0 && maxiter > tail_at && c.B >= 4096;
     if (two_phase) ensure_list();
+    // Early download (two-phase solve into page-locked output buffers): the problems that finished in phase 1 — the
+    // majority — are final when the tail kernel starts, so the WHOLE slice is converted and copied out on a second
+    // stream while the tail kernel runs; afterwards only the tail's problems are written again, straight into the
+    // caller's buffers through the unified address space (coalesced per problem). The early copy of an unfinished
+    // problem holds an intermediate iterate and is overwritten; the order is enforced by pev_early.
+    // CROCODDYL_B200_TPP_EARLY_DOWNLOAD=0 disables it (the copies back then follow the tail kernel).
+    const char* ede = getenv("CROCODDYL_B200_TPP_EARLY_DOWNLOAD");
+    double* m_xs_out = mapped_host(h_xs_out);
+    double* m_us_out = mapped_host(h_us_out);
+    const bool early = two_phase && !(ede && atoi(ede) == 0) && (h_xs_out || h_us_out) && (!h_xs_out || m_xs_out) &&
+                       (!h_us_out || m_us_out);
+    if (early)
+      for (int k = 0; k < K; ++k)
+        if (!dstream[k]) {
+          CGX_CUDA(cudaStreamCreateWithFlags(&dstream[k], cudaStreamNonBlocking));
+          CGX_CUDA(cudaEventCreateWithFlags(&pev_phase1[k], cudaEventDisableTiming));
+          CGX_CUDA(cudaEventCreateWithFlags(&pev_early[k], cudaEventDisableTiming));
+        }
     int cb0 = 0;
     for (int k = 0; k < K; ++k) {
       const int b0 = k * per;
@@ -241,6 +271,7 @@ struct TppBackend : Backend {
                        nullptr, b0, b0 + nb);
         tpp_compact_count_kernel<<<cb, 1024, 0, st>>>(fin, nb, cnt);
         tpp_compact_scatter_kernel<<<cb, 1024, 0, st>>>(fin, nb, cnt, d_list + b0, nact, b0);
+        if (early) CGX_CUDA(cudaEventRecord(pev_phase1[k], st));
         TPP_LAUNCH_BOX(tpp_solve_tail_kernel, ((nb + 31) / 32, 32, 0, st), c, maxiter, is_feasible, reginit, 0, 0, d_list + b0, nact, 0,
                        nb);
         last_launches += 4;
@@ -260,11 +291,35 @@ struct TppBackend : Backend {
       cudaStream_t st = pstream[k];
       const size_t ox = (size_t)b0 * (T + 1) * N, nx = (size_t)nb * (T + 1) * N * sizeof(double);
       const size_t ou = (size_t)b0 * T * U, nu = (size_t)nb * T * U * sizeof(double);
-      if (h_xs_out) {
+      if (early) {
+        cudaStream_t ds = dstream[k];
+        CGX_CUDA(cudaStreamWaitEvent(ds, pev_phase1[k], 0));
+        if (h_xs_out) {
+          gather(d_out_xs + ox, fx.fm, fx.a, fx.b, fx.sel, fx.flip, b0, nb, 0, ds);
+          CGX_CUDA(cudaMemcpyAsync(h_xs_out + ox, d_out_xs + ox, nx, cudaMemcpyDeviceToHost, ds));
+        }
+        if (h_us_out) {
+          gather(d_out_us + ou, fu.fm, fu.a, fu.b, fu.sel, fu.flip, b0, nb, 0, ds);
+          CGX_CUDA(cudaMemcpyAsync(h_us_out + ou, d_out_us + ou, nu, cudaMemcpyDeviceToHost, ds));
+        }
+        CGX_CUDA(cudaEventRecord(pev_early[k], ds));
+        // the tail's problems, after the tail kernel AND after the early copy of this slice has landed
+        CGX_CUDA(cudaStreamWaitEvent(st, pev_early[k], 0));
+        const int gl = nb < 4096 ? nb : 4096;
+        if (h_xs_out) {
+          tpp_gather_list_kernel<<<gl, 128, 0, st>>>(m_xs_out, fx.a, fx.b, fx.sel, fx.flip, fx.fm, c.Bp, d_list + b0, d_list + c.Bp + (c.B + 1023) / 1024 + PIPE_MAX + 1 + k);
+          ++last_launches;
+        }
+        if (h_us_out) {
+          tpp_gather_list_kernel<<<gl, 128, 0, st>>>(m_us_out, fu.a, fu.b, fu.sel, fu.flip, fu.fm, c.Bp, d_list + b0, d_list + c.Bp + (c.B + 1023) / 1024 + PIPE_MAX + 1 + k);
+          ++last_launches;
+        }
+      }
+      if (h_xs_out && !early) {
         gather(d_out_xs + ox, fx.fm, fx.a, fx.b, fx.sel, fx.flip, b0, nb, 0, st);
         CGX_CUDA(cudaMemcpyAsync(h_xs_out + ox, d_out_xs + ox, nx, cudaMemcpyDeviceToHost, st));
       }
-      if (h_us_out) {
+      if (h_us_out && !early) {
         gather(d_out_us + ou, fu.fm, fu.a, fu.b, fu.sel, fu.flip, b0, nb, 0, st);
         CGX_CUDA(cudaMemcpyAsync(h_us_out + ou, d_out_us + ou, nu, cudaMemcpyDeviceToHost, st));
       }

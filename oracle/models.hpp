@@ -151,6 +151,109 @@ struct ActionModelLQR : ActionModel {
 };
 
 // ---------------------------------------------------------------------------------------------
+// IntegratedActionModelEuler(DifferentialActionModelLQR(nq, nu, drift_free), dt) — diff-lqr.hxx:14-88 evaluated first,
+// then the semi-implicit Euler step of euler.hxx:40-131 on a vector-space state (Jintegrate = identity). dt = 0 is the
+// reference's enable_integration_ = false branch (euler.hxx:32-34,70-74,122-130).
+struct ActionModelEulerDiffLQR : ActionModel {
+  int nq;
+  bool drift_free;
+  double dt;
+  Mat Fq, Fv, Fu, Lxx, Lxu, Luu;
+  Vec f0, lx, lu;
+  ActionModelEulerDiffLQR(int nq_, int nu_, bool drift_free_, double dt_)
+      : ActionModel(2 * nq_, nu_, 0), nq(nq_), drift_free(drift_free_), dt(dt_) {
+    Fq = identity(nq, nq);     // diff-lqr.hxx:19
+    Fv = identity(nq, nq);     // :20
+    Fu = identity(nq, nu_);    // :21
+    f0.assign(nq, 1.);         // :22
+    Lxx = identity(nx, nx);    // :23
+    Lxu = identity(nx, nu_);   // :24
+    Luu = identity(nu_, nu_);  // :25
+    lx.assign(nx, 1.);         // :26
+    lu.assign(nu_, 1.);        // :27
+  }
+  // differential model: xout and cost (diff-lqr.hxx:48-57)
+  double diff_calc(const Vec& x, const Vec& u, Vec& xout) const {
+    Vec q(x.begin(), x.begin() + nq), v(x.begin() + nq, x.end());
+    Vec a, b, c;
+    gemv(Fq, q, a);
+    gemv(Fv, v, b);
+    gemv(Fu, u, c);
+    xout.assign(nq, 0.);
+    for (int i = 0; i < nq; ++i) xout[i] = drift_free ? (a[i] + b[i] + c[i]) : (a[i] + b[i] + c[i] + f0[i]);
+    Vec Lxx_x, Luu_u, Lxu_u;
+    gemv(Lxx, x, Lxx_x);
+    gemv(Luu, u, Luu_u);
+    gemv(Lxu, u, Lxu_u);
+    return 0.5 * dot(x, Lxx_x) + 0.5 * dot(u, Luu_u) + dot(x, Lxu_u) + dot(lx, x) + dot(lu, u);
+  }
+  void calc(ActionData& d, const Vec& x, const Vec& u) override {
+    check(x, u);
+    Vec acc;
+    const double cost = diff_calc(x, u, acc);
+    if (dt != 0.) {  // euler.hxx:65-69
+      const double dt2 = dt * dt;
+      for (int i = 0; i < nq; ++i) {
+        const double dq = x[nq + i] * dt + acc[i] * dt2;
+        const double dv = acc[i] * dt;
+        d.xnext[i] = x[i] + dq;
+        d.xnext[nq + i] = x[nq + i] + dv;
+      }
+      d.cost = dt * cost;
+    } else {  // euler.hxx:70-74
+      d.xnext = x;
+      d.cost = cost;
+    }
+  }
+  void calcDiff(ActionData& d, const Vec& x, const Vec& u) override {
+    check(x, u);
+    // differential derivatives (diff-lqr.hxx:76-84)
+    Vec a, b, Lx(nx), Lu(nu);
+    gemv(Lxx, x, a);
+    gemv(Lxu, u, b);
+    for (int i = 0; i < nx; ++i) Lx[i] = lx[i] + a[i] + b[i];
+    Vec c(nu, 0.), e;
+    gemtv_add(Lxu, x, c);
+    gemv(Luu, u, e);
+    for (int i = 0; i < nu; ++i) Lu[i] = lu[i] + c[i] + e[i];
+    d.Fx.setZero();
+    d.Fu.setZero();
+    if (dt != 0.) {  // euler.hxx:100-121
+      const double dt2 = dt * dt;
+      for (int j = 0; j < nq; ++j)
+        for (int i = 0; i < nq; ++i) {
+          d.Fx(i, j) = Fq(i, j) * dt2;
+          d.Fx(i, nq + j) = Fv(i, j) * dt2;
+          d.Fx(nq + i, j) = Fq(i, j) * dt;
+          d.Fx(nq + i, nq + j) = Fv(i, j) * dt;
+        }
+      for (int j = 0; j < nu; ++j)
+        for (int i = 0; i < nq; ++i) {
+          d.Fu(i, j) = Fu(i, j) * dt2;
+          d.Fu(nq + i, j) = Fu(i, j) * dt;
+        }
+      for (int i = 0; i < nq; ++i) d.Fx(i, nq + i) += dt;
+      for (int i = 0; i < nx; ++i) d.Fx(i, i) += 1.;  // Jintegrate(first, addto) on a vector space
+      for (int i = 0; i < nx; ++i) d.Lx[i] = dt * Lx[i];
+      for (int i = 0; i < nu; ++i) d.Lu[i] = dt * Lu[i];
+      for (int j = 0; j < nx; ++j)
+        for (int i = 0; i < nx; ++i) d.Lxx(i, j) = dt * Lxx(i, j);
+      for (int j = 0; j < nu; ++j)
+        for (int i = 0; i < nx; ++i) d.Lxu(i, j) = dt * Lxu(i, j);
+      for (int j = 0; j < nu; ++j)
+        for (int i = 0; i < nu; ++i) d.Luu(i, j) = dt * Luu(i, j);
+    } else {  // euler.hxx:122-130
+      for (int i = 0; i < nx; ++i) d.Fx(i, i) = 1.;
+      d.Lx = Lx;
+      d.Lu = Lu;
+      d.Lxx = Lxx;
+      d.Lxu = Lxu;
+      d.Luu = Luu;
+    }
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
 // ActionModelUnicycle — unicycle.hxx:13-73; data ctor sets Fx = I once (unicycle.hpp:78-80)
 struct ActionModelUnicycle : ActionModel {
   double dt;

@@ -17,7 +17,7 @@ using namespace oracle;
 
 namespace {
 
-enum { KIND_LQR = 0, KIND_UNICYCLE = 1, KIND_ARM = 2 };
+enum { KIND_LQR = 0, KIND_UNICYCLE = 1, KIND_ARM = 2, KIND_EULER_DIFFLQR = 3 };
 enum { SOLVER_DDP = 0, SOLVER_FDDP = 1, SOLVER_BOXDDP = 2, SOLVER_BOXFDDP = 3 };
 
 struct Batch {
@@ -40,6 +40,31 @@ std::shared_ptr<ActionModel> make_lqr(int n, int m, const double* p) {
   take(M->Fx.d.data(), (size_t)n * n);
   take(M->Fu.d.data(), (size_t)n * m);
   take(M->f0.data(), n);
+  take(M->Lxx.d.data(), (size_t)n * n);
+  take(M->Lxu.d.data(), (size_t)n * m);
+  take(M->Luu.d.data(), (size_t)m * m);
+  take(M->lx.data(), n);
+  take(M->lu.data(), m);
+  return M;
+}
+
+// [dt, drift_free, Fq(nq*nq), Fv(nq*nq), Fu(nq*m), f0(nq), Lxx(n*n), Lxu(n*m), Luu(m*m), lx(n), lu(m)], column-major
+size_t difflqr_param_count(int n, int m) {
+  const size_t nq = n / 2;
+  return 2 + 2 * nq * nq + nq * m + nq + (size_t)n * n + (size_t)n * m + (size_t)m * m + n + m;
+}
+std::shared_ptr<ActionModel> make_euler_difflqr(int n, int m, const double* p) {
+  const int nq = n / 2;
+  std::shared_ptr<ActionModelEulerDiffLQR> M = std::make_shared<ActionModelEulerDiffLQR>(nq, m, p[1] != 0.0, p[0]);
+  const double* q = p + 2;
+  auto take = [&](double* dst, size_t cnt) {
+    std::memcpy(dst, q, cnt * sizeof(double));
+    q += cnt;
+  };
+  take(M->Fq.d.data(), (size_t)nq * nq);
+  take(M->Fv.d.data(), (size_t)nq * nq);
+  take(M->Fu.d.data(), (size_t)nq * m);
+  take(M->f0.data(), nq);
   take(M->Lxx.d.data(), (size_t)n * n);
   take(M->Lxu.d.data(), (size_t)n * m);
   take(M->Luu.d.data(), (size_t)m * m);
@@ -72,6 +97,7 @@ extern "C" {
 // params layout:
 //   LQR      : [drift_free, Fx(n*n), Fu(n*m), f0(n), Lxx(n*n), Lxu(n*m), Luu(m*m), lx(n), lu(m)]  column-major
 //   UNICYCLE : [dt, w_x, w_u]
+//   EULER_DIFFLQR : [dt, drift_free, Fq, Fv, Fu, f0, Lxx, Lxu, Luu, lx, lu]  (difflqr_param_count)
 //   ARM      : see arm.hpp (arm_param_count)
 // per_problem_params != 0: params holds B consecutive blocks; else one shared block.
 // tparams (may be NULL): parameter block(s) of the TERMINAL model, same layout / count / per-problem-ness as params
@@ -118,6 +144,10 @@ void* orc_batch_create2(int kind, int solver_kind, int B, int T, int nx, int nu,
             ut->cost_weights[1] = q[2];
             term = ut;
           }
+        } else if (kind == KIND_EULER_DIFFLQR) {
+          if (nx % 2 || (size_t)nparams != difflqr_param_count(nx, nu)) throw std::invalid_argument("DiffLQR params: wrong count");
+          run = term = make_euler_difflqr(nx, nu, p);
+          if (tparams) term = make_euler_difflqr(nx, nu, tparams + (per_problem_params ? (size_t)b * nparams : 0));
         } else if (kind == KIND_ARM) {
           make_arm_models(p, nparams, nx, nu, run, term);
           if (tparams) {  // the terminal block is used as given (its own dt, weights, frame reference)

@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-KIND = {"lqr": 0, "unicycle": 1, "arm": 2}
+KIND = {"lqr": 0, "unicycle": 1, "arm": 2, "euler_difflqr": 3}
 SOLVER = {"ddp": 0, "fddp": 1, "boxddp": 2, "boxfddp": 3}
 SCALARS = ["cost", "stop", "d0", "d1", "xreg", "ureg", "steplength", "dV", "dVexp", "iter", "is_feasible",
            "converged", "n_records", "cost_try", "was_feasible", "_"]

@@ -172,3 +172,40 @@ def test_riccati_sweep_config_c3_sizes():
         assert not ob.backward().any()
         for name in ("K", "k", "Vx", "Vxx"):
             _close(solver.get(name), ob.get_all(name), "%s n=%d" % (name, n))
+
+
+# ------------------------------------------------------------------ DifferentialActionModelLQR on the LQR kernels
+@pytest.mark.parametrize("kind", ["ddp", "fddp"])
+@pytest.mark.parametrize("drift_free", [True, False])
+def test_integrated_euler_of_differential_lqr_against_the_two_step_oracle(kind, drift_free):
+    """IntegratedActionModelEuler(DifferentialActionModelLQR(nq, nu), dt) with a dt = 0 terminal model, solved by the
+    CUDA path (discrete matrices of the Euler step on the LQR kernels, crocoddyl_b200/integrated.py), against the
+    oracle's statement of the reference's two-step evaluation (diff-lqr.hxx:48-84 then euler.hxx:65-130): node
+    quantities through the plugin calls, then the whole solve."""
+    from integrated_cases import oracle_params, random_difflqr
+    nq, nu, B, T, dt = 6, 3, 5, 25, 0.02
+    d, x0 = random_difflqr(nq, nu, B, 21, drift_free)
+    run, term = cb.IntegratedActionModelEuler(d, dt), cb.IntegratedActionModelEuler(d, 0.)
+    problem = cb.ShootingProblem(x0, [run] * T, term)
+    solver = (cb.SolverFDDP if kind == "fddp" else cb.SolverDDP)(problem)
+    ob = ol.OracleBatch("euler_difflqr", kind, T, 2 * nq, nu, oracle_params(d, dt), x0, tparams=oracle_params(d, 0.))
+    rng = np.random.default_rng(3)
+    xs_r, us_r = rng.standard_normal((B, T + 1, 2 * nq)), rng.standard_normal((B, T, nu))
+    # ShootingProblem::calc / calcDiff on a random trajectory
+    ob.set_candidate(xs_r, us_r, False)
+    ob.calc()
+    ob.calcdiff()
+    costs = problem.calc(xs_r, us_r)
+    _close(costs, np.array([sum(ob.get("node_cost", b, t)[0] for t in range(T + 1)) for b in range(B)]), "cost")
+    problem.calcDiff(xs_r, us_r)
+    for name in ("Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu"):
+        for b in (0, B - 1):
+            for t in (0, T // 2, T):
+                if t == T and name in ("Fu", "Lu", "Lxu", "Luu"):
+                    continue  # control derivatives of the terminal node are not used (action-base.hxx:27-37)
+                _close(problem.data(name, b, t), ob.get(name, b, t), "%s b=%d t=%d" % (name, b, t))
+    xs = np.repeat(x0[:, None, :], T + 1, 1)
+    us = np.zeros((B, T, nu))
+    conv = solver.solve(xs, us, 30, False, 1e-9)
+    ob.solve(xs, us, 30, False, 1e-9)
+    _compare_solve(solver, ob, conv)

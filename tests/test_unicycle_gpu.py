@@ -274,6 +274,39 @@ def test_sliced_host_pipeline_equals_sequential_solve(kind, monkeypatch):
     np.testing.assert_allclose(us0[-nb:], ob2.get_all("us"), **TOL)
 
 
+@pytest.mark.parametrize("tail_at", ["3", "22"])
+def test_early_download_into_page_locked_buffers_is_bit_identical(tail_at, monkeypatch):
+    """With page-locked output buffers the sliced pipeline copies every slice out while its tail kernel still runs and
+    then rewrites the tail's problems straight into the caller's buffers (TppBackend::solve_pipelined). What arrives
+    must be bit-identical to the accessors and to the path without the early copy — with a cut after 3 iterations almost
+    every problem is in the tail, with the default cut only the slow ones."""
+    import ctypes as C
+    import torch
+    B, T = 4 * 1024 + 37, 20
+    x0, problem, solver, ob = _pair("fddp", B, T, 5)
+    xs = np.repeat(x0[:, None, :], T + 1, 1)
+    us = np.zeros((B, T, 2))
+    monkeypatch.setenv("CROCODDYL_B200_TPP_TAIL_AT", tail_at)
+    monkeypatch.setenv("CROCODDYL_B200_TPP_EARLY_DOWNLOAD", "0")
+    conv0, xs0, us0 = solver.solveFetch(xs, us, 40, False, 1e-9)
+    n_it = solver.scalars()["n_records"]
+    assert (n_it > int(tail_at)).sum() > (1000 if tail_at == "3" else 0)  # the tail is populated
+    monkeypatch.setenv("CROCODDYL_B200_TPP_EARLY_DOWNLOAD", "1")
+    xs_h, us_h = torch.from_numpy(xs).pin_memory(), torch.from_numpy(us).pin_memory()
+    xs_o = torch.full_like(xs_h, float("nan")).pin_memory()
+    us_o = torch.full_like(us_h, float("nan")).pin_memory()
+    dp = lambda t: C.cast(t.data_ptr(), C.POINTER(C.c_double))  # noqa: E731
+    conv = np.zeros(B, dtype=np.uint8)
+    for _ in range(2):  # twice: the second call finds the first call's results in the buffers
+        cb.check(cb.lib().cgx_solver_solve_fetch(solver._h, dp(xs_h), dp(us_h), 40, 0, 1e-9,
+                                                 conv.ctypes.data_as(C.POINTER(C.c_ubyte)), dp(xs_o), dp(us_o)))
+        assert np.array_equal(conv.astype(bool), conv0)
+        assert np.array_equal(xs_o.numpy(), xs0) and np.array_equal(us_o.numpy(), us0)
+        assert np.array_equal(xs_o.numpy(), solver.xs) and np.array_equal(us_o.numpy(), solver.us)
+        xs_o.fill_(float("nan"))
+        us_o.fill_(float("nan"))
+
+
 def test_solve_fetch_on_the_cta_backend_falls_back_to_sequence():
     """Arm / LQR (CTA-per-problem backend) have no sliced pipeline: solve_fetch = solve + get_all."""
     n, m, T, B = 6, 2, 5, 3

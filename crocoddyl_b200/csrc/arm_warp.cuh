@@ -98,9 +98,7 @@ __device__ void arm_calc_warp(const double* params, bool terminal, const double*
 #pragma unroll
     for (int i = 1; i < NV; ++i)
       if (i <= fp) oM = compose(oM, ld_se3(W.X[i]));
-    FrameRes fr;
-    fr.rMf = actInv(P.Mref(), compose(oM, P.frame_placement()));
-    fr.r = log6(fr.rMf, fr.theta, fr.w);
+    const FrameRes fr = frame_residual_at(P, compose(oM, P.frame_placement()));
     W.cost = diff_cost<NV>(P, fr, x, u);
   }
   __syncwarp();
@@ -122,7 +120,7 @@ __device__ void arm_calc_warp(const double* params, bool terminal, const double*
 #pragma unroll
       for (int k = 0; k < 6; ++k) Uall[k] = __shfl_sync(M6, Ur, k);
       const double pa3 = __shfl_sync(M6, pa, 3), pa4 = __shfl_sync(M6, pa, 4), pa5 = __shfl_sync(M6, pa, 5);
-      const double D = ax.x * Uall[3] + ax.y * Uall[4] + ax.z * Uall[5];
+      const double D = ax.x * Uall[3] + ax.y * Uall[4] + ax.z * Uall[5] + P.armature(i);  // rb::aba
       const double Dinv = 1. / D;
       const double ui = (u ? u[i] : 0.) - (ax.x * pa3 + ax.y * pa4 + ax.z * pa5);
       W.U[i][r] = Ur;

@@ -175,7 +175,7 @@ int cgx_set_device(int device) {
   CGX_CATCH
 }
 
-long cgx_arm_param_count(int nv) { return 32 + 25L * nv; }
+long cgx_arm_param_count(int nv) { return 36 + 28L * nv; }
 
 int cgx_problem_create(cgx_problem_t* out, int kind, int B, int T, int nx, int nu, const double* params,
                        long nparams, int per_problem_params, const double* x0s) {

@@ -255,8 +255,10 @@ CGX_HD M3 rotAxis(const V3& a, double q) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Parameter block of the arm model (include/crocoddyl_b200.h "ARM"): 32 header doubles + 25 per joint.
-constexpr int ARM_HEADER = 32, ARM_PER_JOINT = 25;
+// Parameter block of the arm model (include/crocoddyl_b200.h "ARM"): 36 header doubles + 28 per joint.
+constexpr int ARM_HEADER = 36, ARM_PER_JOINT = 28;
+// goal cost of the frame (header [32]): CostModelFramePlacement / FrameTranslation / FrameRotation
+constexpr int GOAL_PLACEMENT = 0, GOAL_TRANSLATION = 1, GOAL_ROTATION = 2;
 CGX_HD SE3 read_se3(const double* p) {
   SE3 M;
 #pragma unroll
@@ -274,12 +276,18 @@ struct ArmParams {
   CGX_HD int frame_parent() const { return (int)p[7]; }
   CGX_HD SE3 frame_placement() const { return read_se3(p + 8); }
   CGX_HD SE3 Mref() const { return read_se3(p + 20); }
+  CGX_HD int goal_kind() const { return (int)p[32]; }
   CGX_HD const double* joint(int i) const { return p + ARM_HEADER + ARM_PER_JOINT * i; }
   CGX_HD V3 axis(int i) const {
     const double* j = joint(i);
     return V3{j[0], j[1], j[2]};
   }
   CGX_HD SE3 placement(int i) const { return read_se3(joint(i) + 3); }
+  // rotor inertia seen at joint i (free-fwddyn.hxx:66-74: M.diagonal() += armature); 0 = none
+  CGX_HD double armature(int i) const { return joint(i)[25]; }
+  // ActivationModelWeightedQuad weights of the state cost for q_i and v_i (weighted-quadratic.hpp:39-49); 1 = plain quad
+  CGX_HD double wq(int i) const { return joint(i)[26]; }
+  CGX_HD double wv(int i) const { return joint(i)[27]; }
   CGX_HD Inertia inertia(int i) const {
     const double* j = joint(i);
     Inertia Y;
@@ -335,7 +343,9 @@ CGX_HD void aba(const ArmParams& P, const double* q, const double* qd, const dou
     I6 Ia = i6_from(Y) + Iacc;
     const Sp pa = crossF(k.v[i], mulI(Y, k.v[i])) + pacc;
     U[i] = Sp{mul(Ia.B, ax), mul(Ia.C, ax)};
-    const double D = dot(ax, U[i].ang);
+    // joint-space pivot; the armature (rotor inertia) adds to it, which makes the sweep the solution of
+    // (M + diag(armature)) qdd = tau - nle, the system free-fwddyn.hxx:66-74 solves through Minv
+    const double D = dot(ax, U[i].ang) + P.armature(i);
     Dinv[i] = 1. / D;
     u[i] = (tau ? tau[i] : 0.) - dot(ax, pa.ang);
     if (i > 0) {
@@ -661,17 +671,53 @@ CGX_HD void Jlog6(const SE3& M, double t, const V3& w, M3& A, M3& Bm) {
 
 // residual of the frame-placement cost and what its derivative needs
 struct FrameRes {
-  SE3 rMf;
-  Sp r;
+  SE3 rMf;  // placement: Mref^-1 oMf; rotation: R = Rref^T oRf; translation: R = oRf
+  Sp r;     // residual as [linear; angular], the unused half zero
   double theta;
   V3 w;
 };
+// residual of the goal cost of the frame placed at oMf: CostModelFramePlacement (frame-placement.hxx:52-64),
+// CostModelFrameTranslation (frame-translation.hxx:51-61) or CostModelFrameRotation (frame-rotation.hxx:51-65)
+CGX_HD FrameRes frame_residual_at(const ArmParams& P, const SE3& oMf) {
+  FrameRes fr;
+  const int kind = P.goal_kind();
+  if (kind == GOAL_TRANSLATION) {
+    const SE3 ref = P.Mref();
+    fr.rMf = SE3{oMf.R, V3{0., 0., 0.}};
+    fr.r = Sp{oMf.p - ref.p, V3{0., 0., 0.}};
+    fr.theta = 0.;
+    fr.w = V3{0., 0., 0.};
+  } else if (kind == GOAL_ROTATION) {
+    fr.rMf = SE3{mulAtB(P.Mref().R, oMf.R), V3{0., 0., 0.}};  // oRf_inv_ * oRf
+    fr.w = log3(fr.rMf.R, fr.theta);
+    fr.r = Sp{V3{0., 0., 0.}, fr.w};
+  } else {
+    fr.rMf = actInv(P.Mref(), oMf);  // oMf_inv_ * oMf (frame-placement.hxx:58)
+    fr.r = log6(fr.rMf, fr.theta, fr.w);
+  }
+  return fr;
+}
 template <int NV>
 CGX_HD FrameRes frame_residual(const ArmParams& P, const Kin<NV>& k) {
-  FrameRes fr;
-  fr.rMf = actInv(P.Mref(), frame_placement<NV>(P, k));  // oMf_inv_ * oMf (frame-placement.hxx:58)
-  fr.r = log6(fr.rMf, fr.theta, fr.w);
-  return fr;
+  return frame_residual_at(P, frame_placement<NV>(P, k));
+}
+// d r / d q = [[A, Bm], [0, C]] fJf with fJf = getFrameJacobian(LOCAL) as [linear; angular] rows:
+// placement: Jlog6(rMf) (frame-placement.hxx:75-76); translation: oRf * fJf.topRows(3) (frame-translation.hxx:71-72);
+// rotation: Jlog3(rRf) * fJf.bottomRows(3) (frame-rotation.hxx:76-78)
+CGX_HD void frame_residual_jacobian(const ArmParams& P, const FrameRes& fr, M3& A, M3& Bm, M3& C) {
+  const int kind = P.goal_kind();
+  if (kind == GOAL_TRANSLATION) {
+    A = fr.rMf.R;
+    Bm = zero3();
+    C = zero3();
+  } else if (kind == GOAL_ROTATION) {
+    A = zero3();
+    Bm = zero3();
+    C = Jlog3(fr.theta, fr.w);
+  } else {
+    Jlog6(fr.rMf, fr.theta, fr.w, A, Bm);
+    C = A;
+  }
 }
 // differential cost (cost-sum.hxx:103-118, in name order); u == nullptr: zeros
 template <int NV>
@@ -685,7 +731,7 @@ CGX_HD double diff_cost(const ArmParams& P, const FrameRes& fr, const double* x,
     for (int i = 0; i < NV; ++i) c_u += u[i] * u[i];
   }
 #pragma unroll
-  for (int i = 0; i < 2 * NV; ++i) c_x += x[i] * x[i];
+  for (int i = 0; i < 2 * NV; ++i) c_x += x[i] * ((i < NV ? P.wq(i) : P.wv(i - NV)) * x[i]);  // r . (w o r)
   double cost = 0.;
   cost += P.w_gp() * (0.5 * c_gp);
   cost += P.w_u() * (0.5 * c_u);
@@ -751,14 +797,14 @@ CGX_HD void arm_calcdiff_node(const ArmParams& P, bool terminal, const double* x
   // ---- cost derivatives (frame-placement.hxx:68-86: J = Jlog6(rMf) fJf, Lx = J^T r, Lxx = J^T J)
   {
     const FrameRes fr = frame_residual<NV>(P, k);
-    M3 A, Bm;
-    Jlog6(fr.rMf, fr.theta, fr.w, A, Bm);
+    M3 A, Bm, Cb;
+    frame_residual_jacobian(P, fr, A, Bm, Cb);
     double fJf[6 * NV], J[6 * NV];
     frame_jacobian_local<NV>(P, k, fJf);
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
       const V3 l{fJf[0 + 6 * j], fJf[1 + 6 * j], fJf[2 + 6 * j]}, w{fJf[3 + 6 * j], fJf[4 + 6 * j], fJf[5 + 6 * j]};
-      const V3 top = mul(A, l) + mul(Bm, w), bot = mul(A, w);
+      const V3 top = mul(A, l) + mul(Bm, w), bot = mul(Cb, w);
       J[0 + 6 * j] = top.x;
       J[1 + 6 * j] = top.y;
       J[2 + 6 * j] = top.z;
@@ -778,7 +824,8 @@ CGX_HD void arm_calcdiff_node(const ArmParams& P, bool terminal, const double* x
         for (int kk = 0; kk < 6; ++kk) s += J[kk + 6 * j] * r6[kk];
         lx += wgp * s;
       }
-      lx += wx * x[j];
+      const double wj = (j < NV) ? P.wq(j) : P.wv(j - NV);
+      lx += wx * (wj * x[j]);
       Lx[j] = sc * lx;
 #pragma unroll
       for (int i = 0; i < n; ++i) {
@@ -789,7 +836,7 @@ CGX_HD void arm_calcdiff_node(const ArmParams& P, bool terminal, const double* x
           for (int kk = 0; kk < 6; ++kk) s += J[kk + 6 * i] * J[kk + 6 * j];
           lxx += wgp * s;
         }
-        if (i == j) lxx += wx * 1.;
+        if (i == j) lxx += wx * wj;
         const int e = i + n * j;
         q2[e & 1] = sc * lxx;
         if ((e & 1) == 1) st2(Lxx + (e - 1), q2[0], q2[1]);
@@ -817,6 +864,8 @@ CGX_HD void arm_calcdiff_node(const ArmParams& P, bool terminal, const double* x
   {
     double M[NV * NV];
     crba<NV>(P, k, M);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) M[i + NV * i] += P.armature(i);  // free-fwddyn.hxx:69
     spd_inverse<NV>(M, Minv);
   }
 #pragma unroll

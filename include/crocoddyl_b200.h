@@ -75,9 +75,14 @@ CGX_API const char* cgx_version(void);
  *     LQR      [drift_free, Fx(n*n), Fu(n*m), f0(n), Lxx(n*n), Lxu(n*m), Luu(m*m), lx(n), lu(m)]
  *     UNICYCLE [dt, w_x, w_u]                                   (unicycle.hxx:14-15 defaults 0.1, 10, 1)
  *     ARM      [dt, gravity(3), w_gripperPose, w_xReg, w_uReg, frame parent joint, frame placement R(9 row-major) p(3),
- *               Mref R(9) p(3)] + per joint [axis(3), placement in parent R(9) p(3), mass, COM lever(3),
- *               inertia about the COM Ixx Ixy Ixz Iyy Iyz Izz]  = cgx_arm_param_count(nv) = 32 + 25 nv doubles
- *               (the model of benchmark/factory/arm.hpp:60-90; the terminal node is the same model with dt = 0)
+ *               Mref R(9) p(3), goal cost kind, 3 reserved] + per joint [axis(3), placement in parent R(9) p(3), mass,
+ *               COM lever(3), inertia about the COM Ixx Ixy Ixz Iyy Iyz Izz, armature, state-cost weight of q_i, of v_i]
+ *               = cgx_arm_param_count(nv) = 36 + 28 nv doubles
+ *               (the model of benchmark/factory/arm.hpp:60-90; the terminal node is the same model with dt = 0).
+ *               goal cost kind: 0 CostModelFramePlacement (frame-placement.hxx), 1 CostModelFrameTranslation
+ *               (frame-translation.hxx: only Mref p is used), 2 CostModelFrameRotation (frame-rotation.hxx: only Mref R).
+ *               armature: free-fwddyn.hxx:66-74,108-114 (0 = none). State-cost weights: ActivationModelWeightedQuad
+ *               (weighted-quadratic.hpp) on CostModelState; 1 = the plain ActivationModelQuad.
  *   per_problem_params != 0: params holds B consecutive blocks of nparams doubles, else one shared block.
  *   x0s = [B][nx].
  */

@@ -14,14 +14,17 @@
 // Parameter block (doubles), ARM_HEADER + ARM_PER_JOINT * nv:
 //   [0] dt  [1..3] gravity  [4] w_gripperPose  [5] w_xReg  [6] w_uReg  [7] frame parent joint (0-based)
 //   [8..19] frame placement in its parent joint: R (row-major 9), p (3)     [20..31] Mref: R (9), p (3)
-//   per joint: axis (3), placement in parent R (9) p (3), mass, COM lever (3), inertia about COM Ixx Ixy Ixz Iyy Iyz Izz
+//   [32] goal cost: 0 CostModelFramePlacement, 1 CostModelFrameTranslation, 2 CostModelFrameRotation  [33..35] reserved
+//   per joint: axis (3), placement in parent R (9) p (3), mass, COM lever (3), inertia about COM Ixx Ixy Ixz Iyy Iyz Izz,
+//              armature (free-fwddyn.hxx:66-74; any non-zero entry selects the Minv branch), weights of the state
+//              cost for q_i and v_i (ActivationModelWeightedQuad, weighted-quadratic.hpp:39-49; 1 = ActivationModelQuad)
 #pragma once
 #include "models.hpp"
 #include "rbd.hpp"
 
 namespace oracle {
 
-constexpr int ARM_HEADER = 32, ARM_PER_JOINT = 25;
+constexpr int ARM_HEADER = 36, ARM_PER_JOINT = 28;
 inline long arm_param_count(int nv) { return ARM_HEADER + (long)ARM_PER_JOINT * nv; }
 
 template <typename S>
@@ -37,6 +40,9 @@ struct ArmParams {
   rbd::Chain<S> chain;
   S dt, w_gp, w_x, w_u;
   rbd::SE3<S> Mref;
+  int goal = 0;
+  bool has_armature = false;
+  S armature[rbd::MAXNV], wstate[2 * rbd::MAXNV];
   void parse(const double* p, long nparams, int nv) {
     if (nv < 1 || nv > rbd::MAXNV) throw std::invalid_argument("arm: unsupported nv");
     if (nparams != arm_param_count(nv)) throw std::invalid_argument("arm params: wrong count");
@@ -50,6 +56,9 @@ struct ArmParams {
     if (chain.frame_parent < 0 || chain.frame_parent >= nv) throw std::invalid_argument("arm: frame parent out of range");
     chain.frame_placement = read_se3<S>(p + 8);
     Mref = read_se3<S>(p + 20);
+    goal = (int)p[32];
+    if (goal < 0 || goal > 2) throw std::invalid_argument("arm: unknown goal cost");
+    has_armature = false;
     for (int i = 0; i < nv; ++i) {
       const double* j = p + ARM_HEADER + ARM_PER_JOINT * i;
       chain.axis[i] = rbd::V3<S>{S(j[0]), S(j[1]), S(j[2])};
@@ -63,6 +72,10 @@ struct ArmParams {
       I(1, 1) = S(j[22]);
       I(1, 2) = I(2, 1) = S(j[23]);
       I(2, 2) = S(j[24]);
+      armature[i] = S(j[25]);
+      if (j[25] != 0.) has_armature = true;
+      wstate[i] = S(j[26]);
+      wstate[nv + i] = S(j[27]);
     }
   }
 };
@@ -73,14 +86,44 @@ struct ArmEval {
   // calc: acceleration and differential cost (free-fwddyn.hxx:44-80)
   static S calc(const ArmParams<S>& P, rbd::ChainData<S>& d, const S* x, const S* u, S* a, rbd::SE3<S>& rMf, S* r6) {
     const int nv = P.chain.nv;
-    rbd::aba(P.chain, d, x, x + nv, u, a);  // tau = u (full.hpp:44) ; fills oMi (updateGlobalPlacements)
+    if (!P.has_armature) {
+      rbd::aba(P.chain, d, x, x + nv, u, a);  // tau = u (full.hpp:44) ; fills oMi (updateGlobalPlacements)
+    } else {
+      // free-fwddyn.hxx:66-74: M.diagonal() += armature; Minv; xout = Minv (tau - nle)
+      std::vector<S> M(nv * nv), Minv(nv * nv), nle(nv), zero(nv, S(0));
+      rbd::crba(P.chain, d, x, M.data());
+      for (int i = 0; i < nv; ++i) M[i + nv * i] += P.armature[i];
+      if (!rbd::spdInverse(M.data(), nv, Minv.data())) throw std::runtime_error("M + armature is not positive definite");
+      rbd::rnea(P.chain, d, x, x + nv, zero.data(), nle.data());
+      for (int i = 0; i < nv; ++i) {
+        S s = S(0);
+        for (int k = 0; k < nv; ++k) s += Minv[i + nv * k] * (u[k] - nle[k]);
+        a[i] = s;
+      }
+      rbd::aba(P.chain, d, x, x + nv, u, zero.data());  // only for the placements oMi it leaves in d
+    }
     const rbd::SE3<S> oMf = rbd::framePlacement(P.chain, d);
-    rMf = rbd::actInv(P.Mref, oMf);  // oMf_inv_ * oMf   (frame-placement.hxx:58)
-    rbd::toArr(rbd::log6(rMf), r6);
+    for (int i = 0; i < 6; ++i) r6[i] = S(0);
+    if (P.goal == 1) {  // frame-translation.hxx:56: r = oMf.translation - xref
+      rMf = oMf;
+      r6[0] = oMf.p.x - P.Mref.p.x;
+      r6[1] = oMf.p.y - P.Mref.p.y;
+      r6[2] = oMf.p.z - P.Mref.p.z;
+    } else if (P.goal == 2) {  // frame-rotation.hxx:57-58: r = log3(oRf_inv_ * oRf)
+      rMf = rbd::actInv(P.Mref, oMf);
+      S theta;
+      const rbd::V3<S> w = rbd::log3(rMf.R, theta);
+      r6[3] = w.x;
+      r6[4] = w.y;
+      r6[5] = w.z;
+    } else {
+      rMf = rbd::actInv(P.Mref, oMf);  // oMf_inv_ * oMf   (frame-placement.hxx:58)
+      rbd::toArr(rbd::log6(rMf), r6);
+    }
     S c_gp = S(0), c_u = S(0), c_x = S(0);
     for (int i = 0; i < 6; ++i) c_gp += r6[i] * r6[i];
     for (int i = 0; i < nv; ++i) c_u += u[i] * u[i];
-    for (int i = 0; i < 2 * nv; ++i) c_x += x[i] * x[i];
+    for (int i = 0; i < 2 * nv; ++i) c_x += x[i] * (P.wstate[i] * x[i]);  // weighted-quadratic.hpp:47-48
     S cost = S(0);  // cost-sum.hxx:103-118, name order
     cost += P.w_gp * (S(0.5) * c_gp);
     cost += P.w_u * (S(0.5) * c_u);
@@ -128,13 +171,46 @@ struct ActionModelArm : ActionModel {
     ArmEval<double>::calc(P, cd, x.data(), u.data(), a, rMf, r6);  // the data calc left behind (same x, u)
     // dynamics derivatives (free-fwddyn.hxx:103-107): da_dx = [ddq_dq ddq_dv], da_du = Minv
     std::vector<double> dq(nv * nv), dv(nv * nv), Minv(nv * nv);
-    rbd::abaDerivatives(P.chain, cd, x.data(), x.data() + nv, a, dq.data(), dv.data(), Minv.data());
+    if (!P.has_armature) {
+      rbd::abaDerivatives(P.chain, cd, x.data(), x.data() + nv, a, dq.data(), dv.data(), Minv.data());
+    } else {  // free-fwddyn.hxx:108-114: Fx = Minv (-dtau_dq | -dtau_dv) at xout, Fu = Minv, Minv = (M + armature)^-1
+      std::vector<double> M(nv * nv), tq(nv * nv), tv(nv * nv);
+      rbd::crba(P.chain, cd, x.data(), M.data());
+      for (int i = 0; i < nv; ++i) M[i + nv * i] += P.armature[i];
+      if (!rbd::spdInverse(M.data(), nv, Minv.data())) throw std::runtime_error("M + armature is not positive definite");
+      rbd::rneaDerivatives(P.chain, cd, x.data(), x.data() + nv, a, tq.data(), tv.data());
+      for (int j = 0; j < nv; ++j)
+        for (int i = 0; i < nv; ++i) {
+          double s1 = 0, s2 = 0;
+          for (int k = 0; k < nv; ++k) {
+            s1 += Minv[i + nv * k] * tq[k + nv * j];
+            s2 += Minv[i + nv * k] * tv[k + nv * j];
+          }
+          dq[i + nv * j] = -s1;
+          dv[i + nv * j] = -s2;
+        }
+    }
     // cost derivatives (frame-placement.hxx:68-86): J = Jlog6(rMf) * fJf
     double rJf[36];
     std::vector<double> fJf(6 * nv), J(6 * nv);
-    rbd::Jlog6(rMf, rJf);
-    rbd::aba(P.chain, cd, x.data(), x.data() + nv, u.data(), a);  // restore liMi/oMi of the forward dynamics
+    {
+      std::vector<double> scratch(nv);
+      rbd::aba(P.chain, cd, x.data(), x.data() + nv, u.data(), scratch.data());  // restore liMi/oMi of the forward dynamics
+    }
     rbd::frameJacobianLocal(P.chain, cd, fJf.data());
+    for (int e = 0; e < 36; ++e) rJf[e] = 0.;
+    if (P.goal == 1) {  // frame-translation.hxx:71-72: J = oRf * fJf.topRows(3)   (rMf holds oMf here)
+      for (int i = 0; i < 3; ++i)
+        for (int k = 0; k < 3; ++k) rJf[i + 6 * k] = rMf.R(i, k);
+    } else if (P.goal == 2) {  // frame-rotation.hxx:76-78: J = Jlog3(rRf) * fJf.bottomRows(3)
+      double theta;
+      const rbd::V3<double> w = rbd::log3(rMf.R, theta);
+      const rbd::M3<double> J3 = rbd::Jlog3(theta, w);
+      for (int i = 0; i < 3; ++i)
+        for (int k = 0; k < 3; ++k) rJf[(3 + i) + 6 * (3 + k)] = J3(i, k);
+    } else {
+      rbd::Jlog6(rMf, rJf);
+    }
     for (int j = 0; j < nv; ++j)
       for (int i = 0; i < 6; ++i) {
         double s = 0;
@@ -159,9 +235,9 @@ struct ActionModelArm : ActionModel {
       Lu[i] += P.w_u * u[i];
       Luu(i, i) += P.w_u * 1.;
     }
-    for (int i = 0; i < n; ++i) {
-      Lx[i] += P.w_x * x[i];
-      Lxx(i, i) += P.w_x * 1.;
+    for (int i = 0; i < n; ++i) {  // state.hxx:150-160 with Ar = w o r, Arr = diag(w) (weighted-quadratic.hpp:59-63)
+      Lx[i] += P.w_x * (P.wstate[i] * x[i]);
+      Lxx(i, i) += P.w_x * P.wstate[i];
     }
     const double dt = P.dt;
     d.Fx.setZero();

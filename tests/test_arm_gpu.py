@@ -348,3 +348,55 @@ def test_config_c5_full_size_properties():
     g3 = s2.scalars()
     assert np.all(g3["converged"] == 1) and np.all(g3["is_feasible"] == 1)
     assert np.all(g3["cost"] <= g2["cost"] + 1e-9)
+
+
+# ------------------------------------------------------------------ options of the differential model
+_F3_OPTIONS = {
+    "armature": dict(armature=[0.1, 0.2, 0.05, 0.3, 0.15, 0.02, 0.07]),  # examples/arm_manipulation.py:53
+    "weighted_state": dict(xWeights=np.concatenate([np.linspace(0.5, 3., 7), np.linspace(2., 0.1, 7)]), w_xReg=1e-2),
+    "frame_translation": dict(goal="translation"),
+    "frame_rotation": dict(goal="rotation"),
+    "all": dict(armature=[0.1] * 7, xWeights=np.linspace(0.2, 2., 14), w_xReg=1e-3, goal="translation"),
+}
+
+
+@pytest.mark.parametrize("name", sorted(_F3_OPTIONS))
+def test_arm_model_options_node_data_and_solve(name):
+    """Armature branch (free-fwddyn.hxx:66-74,108-114), ActivationModelWeightedQuad on the state cost, CostModelFrame
+    Translation / Rotation as the goal cost: ShootingProblem::calc / calcDiff node data, the quasi-static torques and a
+    whole FDDP solve (thread and warp rollouts) against the oracle, which takes the reference's Minv route for the
+    armature while the kernels add it to the pivots of the articulated-body sweep."""
+    model = _model("synthetic", 7, **_F3_OPTIONS[name])
+    nv, n, T, B = 7, 14, 20, 6
+    rng = np.random.default_rng(5)
+    x0, xs0 = _c4_inputs(model, B, T)
+    problem, solver, ob = _pair("fddp", model, x0, T)
+    xs = np.concatenate([rng.uniform(-1.5, 1.5, (B, T + 1, nv)), rng.standard_normal((B, T + 1, nv))], 2)
+    us = 3. * rng.standard_normal((B, T, nv))
+    ob.set_candidate(xs, us, False)
+    _close(problem.calc(xs, us), ob.calc(), "total cost")
+    problem.calcDiff(xs, us)
+    ob.calcdiff()
+    for b in (0, B - 1):
+        for t in (0, T - 1, T):
+            for f in ("xnext", "Fx", "Fu", "Lx", "Lu", "Lxx", "Luu"):
+                if t == T and f in ("Fu", "Lu", "Luu"):
+                    continue
+                _close(problem.data(f, b, t), ob.get(f, b, t), "%s b=%d t=%d" % (f, b, t))
+            _close(problem.data("cost", b, t), ob.get("node_cost", b, t), "node cost")
+    xr = problem.rollout(us)  # shooting.hxx:198-223 through the rollout kernel (warp-cooperative calc)
+    ob.set_candidate(xr, us, True)
+    ob.calc()
+    for b in (0, B - 1):
+        for t in range(T):
+            _close(xr[b, t + 1], ob.get("xnext", b, t), "rollout")
+    us_q = np.repeat(problem.quasiStatic(x0)[:, None, :], T, 1)
+    solver.enableTrace(100)
+    conv = solver.solve(xs0, us_q, 100, False, 0.1)
+    ob.solve(xs0, us_q, 100, False, 0.1)
+    _compare_solve(solver, ob, conv, rtol=1e-7)
+    for b in range(B):
+        tg, to = solver.trace(b), ob.trace(b)
+        assert tg.shape == to.shape
+        for col in (0, 5, 6, 7, 8, 11, 12):
+            assert np.array_equal(tg[:, col], to[:, col]), (b, col)

@@ -269,6 +269,81 @@ class ActionModelLQR : public ActionModelAbstract {
   VectorXd lx_, lu_;
 };
 
+// DifferentialActionModelLQR(nq, nu, drift_free) — include/crocoddyl/core/actions/diff-lqr.hxx:14-28 (identity / ones
+// defaults): a = Fq q + Fv v + Fu u (+ f0), cost 1/2 [x,u]^T [Lxx Lxu; Lxu^T Luu] [x,u] + lx^T x + lu^T u. Matrices
+// column-major. Put into a problem through IntegratedActionModelEuler below.
+class DifferentialActionModelLQR {
+ public:
+  DifferentialActionModelLQR(std::size_t nq, std::size_t nu, bool drift_free = true)
+      : nq_(nq), nu_(nu), drift_free_(drift_free), Fq(eye(nq, nq)), Fv(eye(nq, nq)), Fu(eye(nq, nu)), f0(nq, 1.),
+        Lxx(eye(2 * nq, 2 * nq)), Lxu(eye(2 * nq, nu)), Luu(eye(nu, nu)), lx(2 * nq, 1.), lu(nu, 1.) {}
+  std::size_t get_nq() const { return nq_; }
+  std::size_t get_nu() const { return nu_; }
+  bool get_drift_free() const { return drift_free_; }
+  MatrixXd Fq, Fv, Fu;
+  VectorXd f0;
+  MatrixXd Lxx, Lxu, Luu;
+  VectorXd lx, lu;
+
+ private:
+  static MatrixXd eye(std::size_t r, std::size_t c) {
+    MatrixXd m(r * c, 0.);
+    for (std::size_t i = 0; i < (r < c ? r : c); ++i) m[i + r * i] = 1.;
+    return m;
+  }
+  std::size_t nq_, nu_;
+  bool drift_free_;
+};
+
+// IntegratedActionModelEuler(DifferentialActionModelLQR, dt) (core/integrator/euler.hxx:41-131 over diff-lqr.hxx:48-84):
+// the semi-implicit Euler step of a linear differential model is linear in (x, u), so the node runs on the LQR kernels
+// with the discrete matrices below, built in the reference's operation order (da * dt^2, da * dt, + dt on the top-right
+// diagonal, + identity; costs scaled by dt; dt = 0: identity step, unscaled cost). A negative dt falls back to 1e-3
+// (euler.hxx:27-31).
+inline std::shared_ptr<ActionModelLQR> IntegratedActionModelEuler(const DifferentialActionModelLQR& d, double dt = 1e-3) {
+  if (dt < 0.) dt = 1e-3;
+  const std::size_t nq = d.get_nq(), nu = d.get_nu(), nx = 2 * nq;
+  auto m = std::make_shared<ActionModelLQR>(nx, nu, d.get_drift_free() || dt == 0.);
+  MatrixXd Fx(nx * nx, 0.), Fu(nx * nu, 0.);
+  VectorXd f0(nx, 0.);
+  const double dt2 = dt * dt, sc = dt != 0. ? dt : 1.;
+  if (dt != 0.) {
+    for (std::size_t j = 0; j < nq; ++j)
+      for (std::size_t i = 0; i < nq; ++i) {
+        Fx[i + nx * j] = d.Fq[i + nq * j] * dt2;
+        Fx[i + nx * (nq + j)] = d.Fv[i + nq * j] * dt2;
+        Fx[(nq + i) + nx * j] = d.Fq[i + nq * j] * dt;
+        Fx[(nq + i) + nx * (nq + j)] = d.Fv[i + nq * j] * dt;
+      }
+    for (std::size_t i = 0; i < nq; ++i) Fx[i + nx * (nq + i)] += dt;
+    for (std::size_t i = 0; i < nx; ++i) Fx[i + nx * i] += 1.;
+    for (std::size_t j = 0; j < nu; ++j)
+      for (std::size_t i = 0; i < nq; ++i) {
+        Fu[i + nx * j] = d.Fu[i + nq * j] * dt2;
+        Fu[(nq + i) + nx * j] = d.Fu[i + nq * j] * dt;
+      }
+    for (std::size_t i = 0; i < nq; ++i) {
+      f0[i] = d.f0[i] * dt2;
+      f0[nq + i] = d.f0[i] * dt;
+    }
+  } else {
+    for (std::size_t i = 0; i < nx; ++i) Fx[i + nx * i] = 1.;
+  }
+  auto scaled = [sc](VectorXd v) {
+    for (double& e : v) e *= sc;
+    return v;
+  };
+  m->set_Fx(Fx);
+  m->set_Fu(Fu);
+  m->set_f0(f0);
+  m->set_Lxx(scaled(d.Lxx));
+  m->set_Lxu(scaled(d.Lxu));
+  m->set_Luu(scaled(d.Luu));
+  m->set_lx(scaled(d.lx));
+  m->set_lu(scaled(d.lu));
+  return m;
+}
+
 // IntegratedActionModelEuler(DifferentialActionModelFreeFwdDynamics(StateMultibody, ActuationModelFull, CostModelSum{
 // gripperPose, xReg, uReg}), dt) on a fixed-base revolute chain (core/integrator/euler.hxx, multibody/actions/
 // free-fwddyn.hxx, benchmark/factory/arm.hpp:60-90): the parameter block of cgx_arm_param_count(nv) doubles

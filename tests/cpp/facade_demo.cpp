@@ -13,10 +13,13 @@ namespace cb = crocoddyl_b200;
 
 int main(int argc, char** argv) {
   const int T = argc > 1 ? atoi(argv[1]) : 20;
-  const bool lqr = argc > 2 && !strcmp(argv[2], "lqr");
+  const bool difflqr = argc > 2 && !strcmp(argv[2], "difflqr");
+  const bool lqr = difflqr || (argc > 2 && !strcmp(argv[2], "lqr"));
   try {
     std::shared_ptr<cb::ActionModelAbstract> model;
-    if (lqr)
+    if (difflqr)  // IntegratedActionModelEuler(DifferentialActionModelLQR(3, 2, drift), dt) on the LQR kernels
+      model = cb::IntegratedActionModelEuler(cb::DifferentialActionModelLQR(3, 2, false), 0.05);
+    else if (lqr)
       model = std::make_shared<cb::ActionModelLQR>(6, 2, true);
     else
       model = std::make_shared<cb::ActionModelUnicycle>();

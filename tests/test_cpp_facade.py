@@ -36,18 +36,25 @@ def test_facade_compiles_and_refuses_without_gpu():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("kind,T", [("unicycle", 20), ("lqr", 15)])
+@pytest.mark.parametrize("kind,T", [("unicycle", 20), ("lqr", 15), ("euler_difflqr", 12)])
 def test_facade_solve_matches_oracle(kind, T):
     exe = _build()
-    r = subprocess.run([exe, str(T)] + (["lqr"] if kind == "lqr" else []), stdout=subprocess.PIPE, text=True)
+    arg = {"unicycle": [], "lqr": ["lqr"], "euler_difflqr": ["difflqr"]}[kind]
+    r = subprocess.run([exe, str(T)] + arg, stdout=subprocess.PIPE, text=True)
     assert r.returncode == 0, r.stdout
     lines = r.stdout.strip().split("\n")
     head = lines[0].split()
     vals = {ln.split()[0]: np.array([float(v) for v in ln.split()[1:]]) for ln in lines[1:4]}
     if kind == "unicycle":
         nx, nu, params, x0 = 3, 2, ol.unicycle_params(), np.array([[-1., -1., 1.]])
-    else:
+    elif kind == "lqr":
         nx, nu, params, x0 = 6, 2, ol.lqr_params(6, 2), np.zeros((1, 6))
+    else:  # the oracle evaluates the differential model first and integrates after, as the reference does
+        from integrated_cases import oracle_params
+        d = cb.DifferentialActionModelLQR(3, 2, False)
+        for name in ("Fq", "Fv", "Fu", "f0", "Lxx", "Lxu", "Luu", "lx", "lu"):
+            setattr(d, name, np.asarray(getattr(d, name))[None])
+        nx, nu, params, x0 = 6, 2, oracle_params(d, 0.05)[0], np.zeros((1, 6))
     ob = ol.OracleBatch(kind, "fddp", T, nx, nu, params, x0)
     ob.solve(np.repeat(x0[:, None, :], T + 1, 1), np.zeros((1, T, nu)), 100, False, 1e-9)
     so = ob.scalars()

@@ -538,21 +538,66 @@ __device__ double cta_calcdiff(const CtaCtx& c, const M& mod, CtaSmem& sm, int b
   return sm.red[0];
 }
 
+// Unblocked lower LLT of Quu (m <= MR <= 32) by ONE warp with lane i holding row i in registers: left-looking, the
+// pivot row's entries reach the other lanes by shuffles, so a step is a chain of multiply-adds without shared-memory
+// round trips or warp barriers. Same operation order as the oracle / Eigen's unblocked LLT (sums over j ascending);
+// x / p as x * (1 / p) unless CGX_PARITY. Writes the factor to sm.Lc; sets *sm.flag when a pivot is not positive.
+// Measured on B200: C1 (LQR 37/12, one problem) 5.03 -> 4.02 ms per call, n = 36 sweep 30.7 -> 24.7 ms, n = 72 sweep
+// 158.1 -> 155.7 ms (there the m = 24 instantiation is 1.5 k straight-line instructions run once per node by one warp:
+// ncu, no_instruction = 71 % of its stalls; a rolled version with predicated register selects was slower still:
+// 229 ms).
+template <int MR>
+__device__ __forceinline__ void cta_llt_warp_regs(CtaSmem& sm, int m, int ldm) {
+  const int lane = threadIdx.x & 31;
+  double row[MR];
+#pragma unroll
+  for (int j = 0; j < MR; ++j) row[j] = (lane < m && j <= lane && j < m) ? sm.Quu[lane + ldm * j] : 0.;
+  bool bad = false;
+#pragma unroll
+  for (int kk = 0; kk < MR; ++kk) {
+    if (kk < m) {
+      double p = row[kk], s = row[kk];
+#pragma unroll
+      for (int j = 0; j < kk; ++j) {
+        const double lkj = __shfl_sync(0xffffffffu, row[j], kk);
+        p -= row[j] * row[j];  // the pivot row's own sum (meaningful on lane kk)
+        s -= row[j] * lkj;
+      }
+      p = __shfl_sync(0xffffffffu, p, kk);
+      if (p <= 0.) bad = true;
+      const double sp = sqrt(p), pinv = 1. / sp;
+      if (lane == kk)
+        row[kk] = sp;
+      else if (lane > kk)
+        row[kk] = div_pivot(s, sp, pinv);
+    }
+  }
+  if (bad && lane == 0) *sm.flag = 1;
+  if (lane < m) {
+#pragma unroll
+    for (int j = 0; j < MR; ++j)
+      if (j <= lane && j < m) sm.Lc[lane + ldm * j] = row[j];
+  }
+}
+
 // K = Quu^-1 Qxu^T, k = Quu^-1 Qu with the right-hand side of a thread in registers (m <= MR): only the factor is read
 // from shared memory (broadcast loads). Same operation order as the in-place version in cta_backward.
 template <int MR>
 __device__ __forceinline__ void cta_solve_rhs_regs(CtaSmem& sm, int n, int m, int ldn, int ldm, int tid, int P) {
   for (int col = tid; col <= n; col += P) {
-    double r[MR];
+    double r[MR], rinv[MR];  // the reciprocal pivots once per right-hand side instead of 2 m divisions (common.cuh)
 #pragma unroll
-    for (int i = 0; i < MR; ++i) r[i] = i < m ? ((col < n) ? sm.Qxu[col + ldn * i] : sm.Qu[i]) : 0.;
+    for (int i = 0; i < MR; ++i) {
+      r[i] = i < m ? ((col < n) ? sm.Qxu[col + ldn * i] : sm.Qu[i]) : 0.;
+      rinv[i] = i < m ? 1. / sm.Lc[i + ldm * i] : 0.;
+    }
 #pragma unroll
     for (int i = 0; i < MR; ++i) {
       if (i < m) {
         double s = r[i];
 #pragma unroll
         for (int j = 0; j < i; ++j) s -= sm.Lc[i + ldm * j] * r[j];
-        r[i] = s / sm.Lc[i + ldm * i];
+        r[i] = div_pivot(s, sm.Lc[i + ldm * i], rinv[i]);
       }
     }
 #pragma unroll
@@ -562,7 +607,7 @@ __device__ __forceinline__ void cta_solve_rhs_regs(CtaSmem& sm, int n, int m, in
 #pragma unroll
         for (int j = i + 1; j < MR; ++j)
           if (j < m) s -= sm.Lc[j + ldm * i] * r[j];
-        r[i] = s / sm.Lc[i + ldm * i];
+        r[i] = div_pivot(s, sm.Lc[i + ldm * i], rinv[i]);
       }
     }
     double* dst = (col < n) ? (sm.Kg + ldm * col) : sm.kg;
@@ -682,7 +727,15 @@ __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, i
         for (int i = tid; i < m; i += P) c.Qu[rnode * m + i] = sm.Qu[i];  // get_Qu returns the clamped gradient
     } else {
     // computeGains (ddp.cpp:298-310): unblocked lower LLT by warp 0
-    if (tid < 32) {
+    if (tid < 32 && m <= 8) {
+      cta_llt_warp_regs<8>(sm, m, ldm);
+    } else if (tid < 32 && m <= 12) {
+      cta_llt_warp_regs<12>(sm, m, ldm);
+    } else if (tid < 32 && m <= 16) {
+      cta_llt_warp_regs<16>(sm, m, ldm);
+    } else if (tid < 32 && m <= 24) {
+      cta_llt_warp_regs<24>(sm, m, ldm);
+    } else if (tid < 32) {
       for (int e = tid; e < m * m; e += 32) sm.Lc[(e % m) + ldm * (e / m)] = sm.Quu[(e % m) + ldm * (e / m)];
       __syncwarp();
       // lane i owns rows i, i+32, ...: left-looking through shared memory. (A register-resident right-looking variant

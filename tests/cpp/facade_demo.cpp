@@ -83,7 +83,9 @@ int main(int argc, char** argv) {
     // control-limited: set_u_lb / set_u_ub on the model, SolverBoxFDDP
     {
       std::shared_ptr<cb::ActionModelAbstract> bm;
-      if (lqr)
+      if (difflqr)
+        bm = cb::IntegratedActionModelEuler(cb::DifferentialActionModelLQR(3, 2, false), 0.05);
+      else if (lqr)
         bm = std::make_shared<cb::ActionModelLQR>(6, 2, true);
       else
         bm = std::make_shared<cb::ActionModelUnicycle>();

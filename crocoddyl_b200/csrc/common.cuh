@@ -58,6 +58,21 @@ __host__ __device__ inline double div_pivot(double x, double p, double pinv) {
 #endif
 }
 
+// Pivot of the unblocked LLT: p -> sqrt(p) and 1 / sqrt(p). The serial chain sqrt -> reciprocal (~2 x 10 dependent FP64
+// instructions) sits on the critical path of every node of the backward sweeps; the default build takes the reciprocal
+// square root directly (rsqrt, <= 1 ulp, the accuracy class of 1 / sqrt(p)) and forms sqrt(p) = p * rsqrt(p), which the
+// default build only stores (all divisions by the pivot are multiplications by the reciprocal, div_pivot above). The
+// parity build keeps the reference's sqrt and division.
+__host__ __device__ inline void llt_pivot(double p, double& sp, double& pinv) {
+#if defined(CGX_PARITY) || !defined(__CUDA_ARCH__)
+  sp = sqrt(p);
+  pinv = 1. / sp;
+#else
+  pinv = rsqrt(p);
+  sp = p * pinv;
+#endif
+}
+
 constexpr int NTRACE = 13;  // matches CGX_NTRACE
 
 }  // namespace cgx

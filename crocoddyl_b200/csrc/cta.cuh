@@ -565,7 +565,8 @@ __device__ __forceinline__ void cta_llt_warp_regs(CtaSmem& sm, int m, int ldm) {
       }
       p = __shfl_sync(0xffffffffu, p, kk);
       if (p <= 0.) bad = true;
-      const double sp = sqrt(p), pinv = 1. / sp;
+      double sp, pinv;
+      llt_pivot(p, sp, pinv);
       if (lane == kk)
         row[kk] = sp;
       else if (lane > kk)

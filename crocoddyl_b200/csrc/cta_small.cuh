@@ -422,8 +422,8 @@ __device__ int cta_backward_warp(const CtaCtx& c, const M& mod, int b, int cur, 
 #pragma unroll
           for (int j = 0; j < kk; ++j) p -= Lr[kk * (kk + 1) / 2 + j] * Lr[kk * (kk + 1) / 2 + j];
           if (p <= 0.) notpd = true;  // a NaN pivot does not fail here; raiseIfNaN catches it below
-          p = sqrt(p);
-          const double pinv = 1. / p;
+          double pinv;
+          llt_pivot(p, p, pinv);
           Lr[kk * (kk + 1) / 2 + kk] = p;
           rinv[kk] = pinv;
 #pragma unroll

@@ -563,9 +563,8 @@ TPP_SWEEP_ATTR int tpp_backward_impl(const TppCtx& c, const M& m, TppStage& stg,
 #pragma unroll
       for (int j = 0; j < kk; ++j) p -= Lc[kk + U * j] * Lc[kk + U * j];
       if (p <= 0.) fail = true;
-      p = sqrt(p);
+      llt_pivot(p, p, Linv[kk]);
       Lc[kk + U * kk] = p;
-      Linv[kk] = 1. / p;
 #pragma unroll
       for (int i = kk + 1; i < U; ++i) {
         double s = Lc[i + U * kk];

@@ -27,7 +27,7 @@ def _digest():
     files = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))] + [os.path.join(root, "include", "crocoddyl_b200.h")]
     for f in files:
         with open(f, "rb") as fh:
-            h.update(f.encode())
+            h.update(os.path.basename(f).encode())  # not the full path: the tree may be checked out anywhere
             h.update(fh.read())
     return h.hexdigest()
 

@@ -67,11 +67,14 @@ def test_stepwise_against_oracle(kind, T, feasible):
 def _compare_solve(solver, ob, conv, B, check_traj=True):
     """Same iteration count, converged flag, regularisation, step length and feasibility per problem; cost/xs/us/K
     within 1e-9. sin/cos on the device differ from glibc's in the last bit for some arguments, and a solve that
-    wanders for ~100 iterations amplifies that until one accept test can flip: such problems (a few in 10,000, see
-    tests/parity_rate.py and DESIGN.md) are counted, bounded, and left out of the value comparison."""
+    wanders for ~100 iterations amplifies that until one accept test can flip. MEASURED on all 65,536 problems of C2
+    (profiles/r02_parity_rate_c2_default.json): 31 differ = 4.7e-4, 27 with the parity build (no FMA contraction, IEEE
+    pivots), 35 when the ORACLE's own sin/cos move by one ulp (profiles/r02_sincos_sensitivity.json) — so this is the
+    floor, not a property of the kernels. At that rate a batch of 256 is expected to hold 0.12 such problems: at most 2
+    are tolerated, they must be long solves, and they are left out of the value comparison."""
     so, sg = ob.scalars(), solver.scalars()
     same = so["n_records"] == sg["n_records"]
-    assert same.mean() >= 0.98, "iteration counts differ on %d of %d problems" % ((~same).sum(), B)
+    assert (~same).sum() <= max(2, int(2e-3 * B)), "iteration counts differ on %d of %d problems" % ((~same).sum(), B)
     assert np.all(so["n_records"][~same] > 60), "a short solve disagrees with the oracle"
     assert np.array_equal(so["converged"].astype(bool)[same], np.atleast_1d(conv)[same])
     assert np.array_equal(so["iter"][same], sg["iter"][same])
@@ -351,17 +354,18 @@ def test_full_size_batch_sampled_against_oracle():
     ob.solve(xs[idx], us[idx], 100, False, 1e-9)
     so = ob.scalars()
     same = so["n_records"] == sg["n_records"][idx]
-    # identical iteration counts are required for (almost) every problem; chaotic non-converging problems may
-    # flip an accept decision on a last-bit tie, so tolerate a tiny fraction and report it
-    assert same.mean() > 0.995, same.mean()
+    # identical iteration counts are required for (almost) every problem. Measured on all 65,536 problems: 4.7e-4 differ
+    # (profiles/r02_parity_rate_c2_default.json), the floor set by the last bit of sin/cos (see _compare_solve): the
+    # 2,048-problem sample is expected to hold ~1, and 6 or more would be a regression
+    assert (~same).sum() <= 5, (~same).sum()
     np.testing.assert_allclose(sg["cost"][idx][same], so["cost"][same], rtol=1e-9)
     ok = same & (so["converged"] == 1)
     # trajectories: 1e-9 relative for (almost) every sampled problem. An OCP that needs many tens of iterations
-    # amplifies last-bit differences (FMA contraction, reciprocal pivots) along its iterates; those few must still
-    # agree to 1e-5 and their share is bounded.
+    # amplifies last-bit differences along its iterates (measured: 99.9 % of the sample within 1e-9, worst 2.4e-7);
+    # those few must still agree to 1e-6 and their share is bounded.
     xo, uo = ob.get_all("xs")[ok], ob.get_all("us")[ok]
     ex = np.abs(xsg[idx][ok] - xo).reshape(xo.shape[0], -1).max(1) / np.maximum(1., np.abs(xo).reshape(xo.shape[0], -1).max(1))
     eu = np.abs(usg[idx][ok] - uo).reshape(uo.shape[0], -1).max(1) / np.maximum(1., np.abs(uo).reshape(uo.shape[0], -1).max(1))
     tight = (ex <= 1e-8) & (eu <= 1e-8)
     assert tight.mean() > 0.998, tight.mean()
-    assert ex.max() < 1e-5 and eu.max() < 1e-5, (ex.max(), eu.max())
+    assert ex.max() < 1e-6 and eu.max() < 1e-6, (ex.max(), eu.max())

@@ -157,9 +157,12 @@ struct TppBackend : Backend {
   // over DRAM pages. So the default stays ONE launch (0); CROCODDYL_B200_TPP_CHUNK=<n> enables the chunked path.
   // iteration after which the unfinished problems of a large batch are compacted and handed to the tail kernel
   // (0 = never). CROCODDYL_B200_TPP_TAIL_AT overrides (development knob).
-  int tail_iter() const {
+  // Measured on B200 (C2, B = 65,536): the resident solve is fastest with the cut at 18-20 (24.2-24.7 ms against 24.9 at
+  // 22 and 25.7 at 30); the sliced host pipeline, whose slices of 16,384 problems leave the machine emptier, prefers a
+  // later cut (e2e 34.4-35.3 ms at 26-28 against 35.2-36.2 at 22).
+  int tail_iter(bool pipelined = false) const {
     const char* e = getenv("CROCODDYL_B200_TPP_TAIL_AT");
-    return e ? atoi(e) : 22;
+    return e ? atoi(e) : (pipelined ? 27 : 19);
   }
   // compaction scratch: [Bp] problem indices, per-1024-block counts (room for PIPE_MAX ragged slices), counters
   void ensure_list() {
@@ -226,7 +229,7 @@ struct TppBackend : Backend {
     CGX_CUDA(cudaEventRecord(ev[1], stream));
     const int per = ((c.B + K - 1) / K + 63) / 64 * 64;
     const Fld fx = fld("xs"), fu = fld("us");
-    const int tail_at = tail_iter();
+    const int tail_at = tail_iter(true);
     const bool two_phase = tail_at > 0 && maxiter > tail_at && c.B >= 4096;
     if (two_phase) ensure_list();
     // Early download (two-phase solve into page-locked output buffers): the problems that finished in phase 1 — the

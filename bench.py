@@ -126,7 +126,39 @@ class ClockSampler(object):
         self.proc = None
         self.index = index
 
+    # NVML first (a thread polling every 5 ms: the timed region of the headline config is ~125 ms, in which
+    # `nvidia-smi -lms 100` delivers one row), nvidia-smi as the fallback
+    NVML_REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
+
+    def _start_nvml(self):
+        import pynvml
+        pynvml.nvmlInit()
+        self.nv = pynvml
+        self.h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+        self.nv_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        self.nv_sm, self.nv_bits, self.nv_stop = [], 0, False
+
+        def poll():
+            get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+            while not self.nv_stop:
+                try:
+                    self.nv_sm.append(float(pynvml.nvmlDeviceGetClockInfo(self.h, pynvml.NVML_CLOCK_SM)))
+                    self.nv_bits |= int(get_reasons(self.h))
+                except Exception:
+                    pass
+                time.sleep(0.005)
+
+        self.th = threading.Thread(target=poll, daemon=True)
+        self.th.start()
+
     def start(self):
+        self.nv = None
+        try:
+            self._start_nvml()
+            return
+        except Exception:
+            self.nv = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
@@ -141,6 +173,12 @@ class ClockSampler(object):
             self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self):
+        if getattr(self, "nv", None) is not None:
+            self.nv_stop = True
+            self.th.join(timeout=1.)
+            reasons = sorted(n for n, bit in self.NVML_REASONS if self.nv_bits & bit)
+            return {"sm_mhz": float(np.median(self.nv_sm)) if self.nv_sm else None, "sm_max_mhz": self.nv_max,
+                    "reasons": reasons, "samples": len(self.nv_sm), "source": "nvml, 5 ms"}
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()

@@ -23,6 +23,7 @@ class ActionModelUnicycle(ActionModelAbstract):
     """ActionModelUnicycle (include/crocoddyl/core/actions/unicycle.hxx:13-73): nx = 3, nu = 2, dt = 0.1,
     costWeights = (10, 1)."""
     kind = MODEL_UNICYCLE
+    writes_residual = True  # data.r = [w0 x; w1 u] (unicycle.hxx:39-40)
 
     def __init__(self):
         self._init_abstract(3, 2, 5)
@@ -195,7 +196,7 @@ class ShootingProblem(object):
 
     def data(self, field, b, t):
         """Field of the ActionData of node t (t == T: terminalData) of problem b."""
-        shp = self._DATA_SHAPES[field](self.ndx, self.nu_max)
+        shp = (self.model.nr,) if field == "r" else self._DATA_SHAPES[field](self.ndx, self.nu_max)
         out = np.zeros(int(np.prod(shp)))
         check(lib().cgx_problem_get_data(self._h, field.encode(), b, t, dptr(out)))
         return out.reshape(shp, order="F")

@@ -33,8 +33,9 @@ class StateVector(object):
 
 class ActionDataAbstract(object):
     """ActionDataAbstract (include/crocoddyl/core/action-base.hpp:101-142): cost, xnext, r, Fx, Fu, Lx, Lu, Lxx, Lxu, Luu.
-    Batched models carry a leading batch dimension on every field. `r` (the cost residual) is allocated with the
-    model's nr like the reference's data but is not exported by the device path."""
+    Batched models carry a leading batch dimension on every field. `r` (the cost residual) is filled where the
+    reference's model writes it: ActionModelUnicycle::calc (unicycle.hxx:39-40). ActionModelLQR has nr = 0, and the
+    reference's cost sum does not write the action data's r for the integrated arm model, so it stays zero there."""
 
     def __init__(self, model):
         n, m = model.ndx, model.nu
@@ -128,7 +129,7 @@ class ActionModelAbstract(object):
             ub = np.zeros((B, self.nu))
         xs = np.repeat(xb[:, None, :], 2, 1)
         prob.calc(xs, ub[:, None, :])
-        self._fill(data, prob, t, one, ("cost", "xnext"))
+        self._fill(data, prob, t, one, ("cost", "xnext") + (("r",) if getattr(self, "writes_residual", False) else ()))
         if diff:
             prob.calcDiff(xs, ub[:, None, :])
             self._fill(data, prob, t, one, ("Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu"))

@@ -144,6 +144,7 @@ struct UnicycleModel {
   static constexpr int NX = 3;
   static constexpr int NU = 2;
   static constexpr int NAUX = 2;  // sin, cos of x[2]: computed by calc, reused by calcDiff (unicycle.hxx:30-31,57-58)
+  static constexpr int NR = 5;    // residual data->r = [w0 x; w1 u] (unicycle.hxx:39-40)
   // Structure of the derivatives (unicycle.hxx:45-73, data ctor unicycle.hpp:78-80): 0 = identically zero, 1 = one,
   // 2 = general. The Riccati products skip the structural zeros (x + 0*y = x for finite y) and do not multiply by the
   // ones, in the reference's summation order: same values, a third of the multiply-adds.
@@ -187,6 +188,13 @@ struct UnicycleModel {
   __device__ double calc(const double* x, const double* u, double* xnext) const {
     double aux[2];
     return calc(x, u, xnext, aux);
+  }
+  // ActionDataAbstract::r as calc leaves it (unicycle.hxx:39-40)
+  __device__ void residual(const double* x, const double* u, double* r) const {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) r[i] = w0 * x[i];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) r[3 + i] = w1 * u[i];
   }
   // calc + calcDiff in one go from the sin / cos calc left in aux. Matrices column-major. (unicycle.hxx:45-73)
   __device__ double calcBothAux(const double* x, const double* u, const double* aux, double* xnext, double* Fx,
@@ -1189,7 +1197,7 @@ __global__ void __launch_bounds__(64) tpp_trystep_kernel(const __grid_constant__
 template <class M>
 __global__ void tpp_node_data_kernel(TppCtx c, const double* __restrict__ xs, const double* __restrict__ us,
                                      int diff, double* cost, double* xnext, double* Fx, double* Fu, double* Lx,
-                                     double* Lu, double* Lxx, double* Lxu, double* Luu) {
+                                     double* Lu, double* Lxx, double* Lxu, double* Luu, double* R) {
   constexpr int N = M::NX, U = M::NU;
   const int T = c.T;
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1206,6 +1214,9 @@ __global__ void tpp_node_data_kernel(TppCtx c, const double* __restrict__ xs, co
   if (!diff) {
     cost[node] = m.calc(x, u, xn);
     for (int i = 0; i < N; ++i) xnext[node * N + i] = xn[i];
+    double r[M::NR];
+    m.residual(x, u, r);
+    for (int i = 0; i < M::NR; ++i) R[node * M::NR + i] = r[i];
   } else {
     m.calcBoth(x, u, xn, fx, fu, lx, lu, lxx, lxu, luu);
     for (int i = 0; i < N * N; ++i) Fx[node * N * N + i] = fx[i];

@@ -27,7 +27,7 @@ struct TppBackend : Backend {
   std::vector<void*> allocs;
   bool solver_allocated = false;
   int* d_list = nullptr;  // compaction: [Bp] problem indices, per-block counts, number of unfinished problems
-  double* node_data[9] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  double* node_data[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
   explicit TppBackend(const ProblemDesc* p_, int sk) {
     p = p_;
@@ -518,12 +518,13 @@ struct TppBackend : Backend {
     if (name == "Lxx") return {N * N, T + 1};
     if (name == "Lxu") return {N * U, T + 1};
     if (name == "Luu") return {U * U, T + 1};
+    if (name == "r") return {M::NR, T + 1};  // ActionDataAbstract::r (action-base.hpp:130), written by calc
     throw NotFound("unknown data field " + name);
   }
   void export_data(const std::string& name, int b, int t, double* d_out) override {
-    static const char* names[9] = {"cost", "xnext", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu"};
+    static const char* names[10] = {"cost", "xnext", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu", "r"};
     FieldInfo fi = data_info(name);
-    for (int i = 0; i < 9; ++i)
+    for (int i = 0; i < 10; ++i)
       if (name == names[i]) {
         if (!node_data[i]) throw InvalidArg("node data not computed yet: call calc / calcDiff first");
         CGX_CUDA(cudaMemcpyAsync(d_out, node_data[i] + ((size_t)b * (c.T + 1) + t) * fi.size,
@@ -607,12 +608,12 @@ void TppBackend<M>::export_trace_all(int nrec, double* d_out) {
 template <class M>
 void TppBackend<M>::problem_calc(const double* d_xs, const double* d_us, int diff, double* d_costs) {
   const size_t nodes = (size_t)c.B * (c.T + 1);
-  const int sizes[9] = {1, N, N * N, N * U, N, U, N * N, N * U, U * U};
-  for (int i = 0; i < 9; ++i)
+  const int sizes[10] = {1, N, N * N, N * U, N, U, N * N, N * U, U * U, M::NR};
+  for (int i = 0; i < 10; ++i)
     if (!node_data[i]) node_data[i] = alloc(nodes * sizes[i]);
   tpp_node_data_kernel<M><<<dim3(nblocks(), c.T + 1), 64, 0, stream>>>(
       c, d_xs, d_us, diff, node_data[0], node_data[1], node_data[2], node_data[3], node_data[4], node_data[5],
-      node_data[6], node_data[7], node_data[8]);
+      node_data[6], node_data[7], node_data[8], node_data[9]);
   ++last_launches;
   tpp_cost_sum_kernel<<<nblocks(), 64, 0, stream>>>(c.B, c.T, node_data[0], d_costs);
   ++last_launches;

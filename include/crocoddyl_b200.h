@@ -116,7 +116,8 @@ CGX_API int cgx_problem_rollout(cgx_problem_t p, const double* us, double* xs);
  * xs_point = [B][nx], us_out = [B][nu] */
 CGX_API int cgx_problem_quasi_static(cgx_problem_t p, const double* xs_point, double* us_out);
 /* ActionDataAbstract fields of node t of problem b after calc/calcDiff (core/action-base.hpp:101-142):
- * field in {"cost","xnext","Fx","Fu","Lx","Lu","Lxx","Lxu","Luu"}; t == T is the terminal data.
+ * field in {"cost","xnext","Fx","Fu","Lx","Lu","Lxx","Lxu","Luu"}; t == T is the terminal data. "r" (the cost residual,
+ * nr doubles) exists where the reference's model writes it: CGX_MODEL_UNICYCLE (nr = 5, unicycle.hxx:39-40), after calc.
  * Returns the number of doubles written (>0) or an error (<0). */
 CGX_API int cgx_problem_get_data(cgx_problem_t p, const char* field, int b, int t, double* out);
 /* ARM parameter block size for an nv-joint chain */

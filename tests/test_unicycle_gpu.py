@@ -167,6 +167,15 @@ def test_problem_calc_calcdiff_rollout():
                 if t == T and f in ("Fx", "Fu", "Lu", "Lxu", "Luu", "xnext"):
                     continue
                 np.testing.assert_allclose(got, ob.get(f, b, t), err_msg=f, **TOL)
+            # ActionDataAbstract::r as ActionModelUnicycle::calc leaves it (unicycle.hxx:39-40): [w0 x; w1 u], cost = r.r / 2
+            r = problem.data("r", b, t)
+            u_t = us[b, t] if t < T else np.zeros(2)
+            np.testing.assert_allclose(r, np.concatenate([10. * xs[b, t], 1. * u_t]), rtol=1e-15)
+            np.testing.assert_allclose(0.5 * r @ r, problem.data("cost", b, t)[0], rtol=1e-14)
+    m1 = cb.ActionModelUnicycle()  # the plugin call fills data.r too
+    d1 = m1.createData()
+    m1.calc(d1, xs[0, 0], us[0, 0])
+    np.testing.assert_allclose(d1.r, np.concatenate([10. * xs[0, 0], us[0, 0]]), rtol=1e-15)
     xr = problem.rollout(us)
     np.testing.assert_allclose(xr[:, 0], x0)
     for t in range(T):  # xs[t+1] = xnext(xs[t], us[t])

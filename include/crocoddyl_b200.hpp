@@ -175,6 +175,8 @@ class ActionModelAbstract {
     check(cgx_problem_calc(node_, xs.data(), us.data(), &c));
     check(cgx_problem_get_data(node_, "cost", 0, t, &d->cost));
     check(cgx_problem_get_data(node_, "xnext", 0, t, d->xnext.data()));
+    // the cost residual, where the reference's model writes it (ActionModelUnicycle::calc, unicycle.hxx:39-40)
+    if (kind() == CGX_MODEL_UNICYCLE && d->r.size() == 5) check(cgx_problem_get_data(node_, "r", 0, t, d->r.data()));
     if (diff) {
       check(cgx_problem_calc_diff(node_, xs.data(), us.data(), &c));
       check(cgx_problem_get_data(node_, "Fx", 0, t, d->Fx.data()));

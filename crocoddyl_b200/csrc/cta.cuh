@@ -618,16 +618,39 @@ __device__ __forceinline__ void cta_solve_rhs_regs(CtaSmem& sm, int n, int m, in
   }
 }
 
+// the 12 / 4 instantiation out of line (see OUTLINE_SMALL at cta_backward)
+template <class M>
+__device__ __noinline__ int cta_backward_warp_12_4(const CtaCtx& c, const M& mod, int b, int cur, bool is_feasible, double xreg,
+                                                   double ureg, double& dg_out, double& dq_out, double& stop_out) {
+  return cta_backward_warp<12, 4>(c, mod, b, cur, is_feasible, xreg, ureg, dg_out, dq_out, stop_out);
+}
+
 // ---------------------------------------------------------------------------------------------
 // SolverDDP::backwardPass + computeGains (ddp.cpp:180-253,298-310) for one problem by the whole block, with the
 // reductions of updateExpectedImprovement (fddp.cpp:126-147) / expectedImprovement (ddp.cpp:144-155) /
 // stoppingCriteria (ddp.cpp:132-142). Returns 0 or 1 ("backward_error") to all threads; dg,dq,stop valid on
 // every thread.
-template <class M>
+// OUTLINE_SMALL: whether the compile-time 12 / 4 instantiation below is called out of line. Measured on B200, same
+// source otherwise: inline, the fused solve kernel's register allocation changes and the single-OCP case C1 (n = 37)
+// goes from 3.7 to 4.6 ms; out of line, the batched sweep kernel slows down (n = 36: 24.2 -> 27.0 ms, n = 72: 148.7 ->
+// 157.2 ms). So the fused solve kernel calls it out of line and the step-wise / phase kernels inline it.
+template <class M, bool OUTLINE_SMALL = false>
 __device__ int cta_backward(const CtaCtx& c, const M& mod, CtaSmem& sm, int b, int cur, bool is_feasible, double xreg,
                             double ureg, double& dg_out, double& dq_out, double& stop_out) {
 #ifndef CGX_NO_SMALL_BACKWARD
-  if (cta_is_small(c.n, c.m)) return cta_backward_warp<M::kN, M::kM>(c, mod, b, cur, is_feasible, xreg, ureg, dg_out, dq_out, stop_out);
+  if (cta_is_small(c.n, c.m)) {
+    // run-time-sized models (LQR): the size of BASELINE config C3 gets the compile-time instantiation (outputs per lane
+    // known, LLT and right-hand sides in registers), the others the run-time loops
+    if constexpr (M::kN == 0) {
+      if (c.n == 12 && c.m == 4) {
+        if constexpr (OUTLINE_SMALL)
+          return cta_backward_warp_12_4(c, mod, b, cur, is_feasible, xreg, ureg, dg_out, dq_out, stop_out);
+        else
+          return cta_backward_warp<12, 4>(c, mod, b, cur, is_feasible, xreg, ureg, dg_out, dq_out, stop_out);
+      }
+    }
+    return cta_backward_warp<M::kN, M::kM>(c, mod, b, cur, is_feasible, xreg, ureg, dg_out, dq_out, stop_out);
+  }
 #endif
   const int T = c.T, n = c.n, m = c.m, ldn = sm.ldn, ldm = sm.ldm;
   const int tid = threadIdx.x, P = blockDim.x;
@@ -1125,7 +1148,7 @@ __global__ void __launch_bounds__(M::kMaxThreads, M::kMinBlocks) cta_solve_kerne
     int retries = 0;
     while (true) {  // computeDirection(recalcDiff) with regularisation retry (ddp.cpp:55-68)
       if (recalc) cost = cta_calcdiff(c, mod, sm, b, cur, iter == 0, feas, wasfeas);
-      const int st = cta_backward(c, mod, sm, b, cur, feas, xreg, ureg, dg, dq, stop);
+      const int st = cta_backward<M, true>(c, mod, sm, b, cur, feas, xreg, ureg, dg, dq, stop);
       ++nbwd;
       if (st == 0) break;
       recalc = false;

@@ -68,3 +68,24 @@ def test_solve_of_the_mapping_equals_the_two_step_model(kind, drift_free):
     for name in ("xs", "us", "K", "k", "Vx", "Vxx"):
         for prob in range(B):
             _close(a.get_all(name, prob), b.get_all(name, prob), name)
+
+
+def test_integrated_euler_of_free_forward_dynamics_is_the_arm_model():
+    """IntegratedActionModelEuler(DifferentialActionModelFreeFwdDynamics(...), dt) — the composition the reference's arm
+    factory writes (benchmark/factory/arm.hpp:76-90) — gives the arm node model with the differential model's options."""
+    chain = cb.synthetic_arm(7)
+    arm = np.linspace(0.1, 0.7, 7)
+    dam = cb.DifferentialActionModelFreeFwdDynamics(chain, armature=arm, goal="translation", w_xReg=1e-3)
+    run = cb.IntegratedActionModelEuler(dam, 2e-3)
+    term = cb.IntegratedActionModelEuler(dam, 0.)
+    assert isinstance(run, cb.ArmActionModel) and run.differential is dam
+    assert run.dt == 2e-3 and term.dt == 0. and run.nx == 14 and run.nu == 7
+    p = run.params()
+    assert p.size == 36 + 28 * 7 and p[0] == 2e-3 and p[32] == 1. and p[5] == 1e-3
+    np.testing.assert_array_equal(p[36 + 25::28], arm)
+    np.testing.assert_array_equal(term.params()[1:], p[1:])  # the same differential model, only dt differs
+    # the oracle accepts the block (layout agreed between the product's host side and the checker)
+    x0 = np.zeros((1, 14))
+    ob = ol.OracleBatch("arm", "fddp", 2, 14, 7, p, x0, tparams=term.params())
+    ob.set_candidate(np.zeros((1, 3, 14)), np.zeros((1, 2, 7)), False)
+    assert np.isfinite(ob.calc()).all()

@@ -209,3 +209,32 @@ def test_integrated_euler_of_differential_lqr_against_the_two_step_oracle(kind, 
     conv = solver.solve(xs, us, 30, False, 1e-9)
     ob.solve(xs, us, 30, False, 1e-9)
     _compare_solve(solver, ob, conv)
+
+
+@pytest.mark.parametrize("name", ["driftfree", "drift"])
+def test_integrated_differential_lqr_node_data_equal_the_reference_vectors(name):
+    """The CUDA path (through the C ABI) against vectors the reference's legacy NumPy classes produced for
+    IntegratedActionModelEuler(DifferentialActionModelLQR) (tests/golden/ref_golden_difflqr.npz): xnext, Fx, Fu as the
+    reference computes them; cost and its derivatives times dt (the C++ integrator scales them, euler.hxx:68,117-121)."""
+    import os
+    G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_golden_difflqr.npz"))
+    pre = "euler_difflqr_%s/" % name
+    c = {k[len(pre):]: G[k] for k in G.files if k.startswith(pre)}
+    dt, N = float(c["dt"]), len(c["x"])
+    d = cb.DifferentialActionModelLQR(3, 2, bool(c["drift_free"]))
+    for k in ("Fq", "Fv", "Fu", "f0", "Lxx", "Lxu", "Luu", "lx", "lu"):
+        setattr(d, k, np.repeat(c["p_" + k][None], N, 0))  # one problem per sample point
+    model = cb.IntegratedActionModelEuler(d, dt)
+    problem = cb.ShootingProblem(c["x"], [model], model)
+    xs = np.repeat(c["x"][:, None, :], 2, 1)
+    us = c["u"][:, None, :]
+    problem.calc(xs, us)
+    problem.calcDiff(xs, us)
+    tol = dict(rtol=1e-12, atol=1e-13)
+    for b in range(N):
+        np.testing.assert_allclose(problem.data("xnext", b, 0), c["xnext"][b], **tol)
+        np.testing.assert_allclose(problem.data("Fx", b, 0), c["Fx"][b], **tol)
+        np.testing.assert_allclose(problem.data("Fu", b, 0), c["Fu"][b], **tol)
+        np.testing.assert_allclose(problem.data("cost", b, 0)[0], dt * c["cost"][b], **tol)
+        for f in ("Lx", "Lu", "Lxx", "Lxu", "Luu"):
+            np.testing.assert_allclose(problem.data(f, b, 0), dt * c[f][b], err_msg=f, **tol)
